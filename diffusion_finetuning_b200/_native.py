@@ -1,0 +1,97 @@
+"""ctypes binding of libb200lora.so (the C-ABI declared in include/b200lora.h).
+
+The library is the ONLY compute path for CUDA tensors: if it is missing or a call fails this
+module raises — there is no eager/PyTorch fallback behind it.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200lora.so")
+
+F32, F16, BF16 = 0, 1, 2
+IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+W_NK, W_KN = 0, 1
+
+_DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
+
+_lib = None
+_lock = threading.Lock()
+
+_vp, _i64, _i32, _f32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+
+# name -> (restype, argtypes); mirrors include/b200lora.h one to one
+SIGNATURES = {
+    "b200lora_version": (_i32, []),
+    "b200lora_last_error": (ctypes.c_char_p, []),
+    "b200lora_tc_supported": (_i32, []),
+    "b200lora_lora_gemm": (_i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i32, _vp, _i64, _i64, _vp, _i64,
+                                  _i64, _i32, _f32, _vp, _i64, _vp, _i64, _i32, _i32, _i32, _i32,
+                                  _i32, _vp]),
+    "b200lora_linear_fwd": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _f32, _vp, _vp, _i64, _i32,
+                                   _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_linear_bwd_dx": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _f32, _vp, _vp, _i64, _i32,
+                                      _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_lora_grads": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32,
+                                   _i32, _i32, _vp, _i64, _vp]),
+    "b200lora_lora_grads_workspace": (_i64, [_i64, _i32, _i32, _i32]),
+    "b200lora_merge": (_i32, [_vp, _vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_absmean_accum": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_svd_epilogue": (_i32, [_vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _vp]),
+}
+
+
+class B200LoraError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) and return the shared library; raise loudly if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise B200LoraError(
+                f"{LIB_PATH} is not built. Run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or `python diffusion_finetuning_b200/build.py`). There is no fallback path.")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def dtype_code(dt):
+    try:
+        return _DTYPE_CODE[dt]
+    except KeyError:
+        raise B200LoraError(f"unsupported dtype {dt}; b200lora handles fp32/fp16/bf16") from None
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().b200lora_last_error().decode(errors="replace")
+        raise B200LoraError(f"{what} failed with code {rc}: {msg}")
+
+
+def stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def require_cuda(t, what):
+    if not t.is_cuda:
+        raise B200LoraError(
+            f"{what}: tensor is on {t.device}; the b200lora hot path is CUDA-only and has no CPU "
+            "fallback. Move the module to a B200 (`.to('cuda')`).")

@@ -1,0 +1,384 @@
+// extern "C" entry points of libb200lora.so (declared in include/b200lora.h).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------------------
+static thread_local char g_err[512] = {0};
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// forward declarations of the per-file launchers
+int tc_pick_bn(int Nout);
+int tc_smem_bytes(int BN, int* stages_out);
+unsigned int tc_read_watchdog();
+template <typename TIO>
+cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const TcParams&,
+                      int, int, cudaStream_t);
+template <typename TIO>
+cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
+                        const void*, long long, long long, const void*, long long, long long, int,
+                        float, void*, long long, void*, long long, int, int, int, cudaStream_t);
+template <typename T>
+cudaError_t launch_grad_reduce(const void*, long long, const void*, int, float, float*, long long,
+                               long long, float*, long long, int, cudaStream_t);
+int grad_reduce_splits(long long M, int C, int esize);
+template <typename TW, typename TL, int MODE>
+cudaError_t launch_merge(const void*, void*, const void*, const void*, float, int, int, int,
+                         float*, cudaStream_t);
+cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, int, int,
+                                cudaStream_t);
+
+// ---------------------------------------------------------------------------------------
+// device info
+// ---------------------------------------------------------------------------------------
+struct DevInfo { int ok, major, minor, sms; };
+static DevInfo dev_info() {
+  static thread_local DevInfo cached[16] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return DevInfo{0, 0, 0, 0};
+  if (!cached[dev].ok) {
+    cudaDeviceProp pr;
+    if (cudaGetDeviceProperties(&pr, dev) != cudaSuccess) return DevInfo{0, 0, 0, 0};
+    cached[dev] = DevInfo{1, pr.major, pr.minor, pr.multiProcessorCount};
+  }
+  return cached[dev];
+}
+
+// ---------------------------------------------------------------------------------------
+// TMA descriptors: cuTensorMapEncodeTiled resolved through the runtime (no -lcuda, so the
+// library also loads on a box without a driver), results cached per (ptr, shape, box).
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct TmKey {
+  const void* ptr; uint64_t d0, d1, ld; uint32_t b0, b1; int dt, sw, dev;
+  bool operator==(const TmKey& o) const { return memcmp(this, &o, sizeof(TmKey)) == 0; }
+};
+struct TmKeyHash {
+  size_t operator()(const TmKey& k) const {
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+    size_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(TmKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+    return h;
+  }
+};
+static std::mutex g_tm_mu;
+static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
+
+// 2-D row-major [rows, cols] 16-bit tensor, box [box_rows, box_cols]
+static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                    uint32_t box_rows, uint32_t box_cols, int dt, CUtensorMapSwizzle sw) {
+  TmKey key;
+  memset(&key, 0, sizeof(key));
+  key.ptr = ptr; key.d0 = cols; key.d1 = rows; key.ld = ld; key.b0 = box_cols; key.b1 = box_rows;
+  key.dt = dt; key.sw = (int)sw;
+  cudaGetDevice(&key.dev);
+  {
+    std::lock_guard<std::mutex> g(g_tm_mu);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return B200LORA_E_CUDA; }
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapDataType cdt =
+      dt == B200LORA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult rc = fn(out, cdt, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed rc=%d (ptr=%p rows=%llu cols=%llu ld=%llu box=%ux%u)",
+              (int)rc, ptr, (unsigned long long)rows, (unsigned long long)cols,
+              (unsigned long long)ld, box_rows, box_cols);
+    return B200LORA_E_CUDA;
+  }
+  std::lock_guard<std::mutex> g(g_tm_mu);
+  if (g_tm_cache.size() > 8192) g_tm_cache.clear();
+  g_tm_cache.emplace(key, *out);
+  return 0;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// can the tcgen05 path take this problem?  (writes the reason to the error slot if not)
+static bool tc_applicable(const void* X, long long ldx, const void* W, long long ldw, int w_layout,
+                          const void* Y, long long ldy, int r, int io_dtype) {
+  if (io_dtype == B200LORA_F32) { set_error("tc path needs 16-bit io"); return false; }
+  if (w_layout != B200LORA_W_NK) { set_error("tc path needs W as [Nout,Kc]"); return false; }
+  if (r < 1 || r > 16) { set_error("tc path needs 1 <= r <= 16"); return false; }
+  if (!aligned16(X) || !aligned16(W) || !aligned16(Y) || (ldx % 8) || (ldw % 8) || (ldy % 8)) {
+    set_error("tc path needs 16-byte aligned pointers and leading dimensions");
+    return false;
+  }
+  DevInfo di = dev_info();
+  if (!di.ok || di.major != 10) { set_error("tc path needs an sm_100 device"); return false; }
+  return true;
+}
+
+static int run_tc(const void* X, long long ldx, const void* W, long long ldw, const void* bias,
+                  int bias_dtype, const void* S1, long long s1_rs, long long s1_cs, const void* S2,
+                  long long s2_rs, long long s2_cs, int ab_dtype, float scale, void* Y,
+                  long long ldy, void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
+                  cudaStream_t stream) {
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
+  p.BN = tc_pick_bn(Nout);
+  p.num_m_blk = (int)((M + 127) / 128);
+  p.num_n_blk = (Nout + p.BN - 1) / p.BN;
+  p.num_k_blk = (Kc + 63) / 64;
+  const int smem = tc_smem_bytes(p.BN, &p.stages);
+  if (p.stages < 2) { set_error("tc: not enough shared memory for BN=%d", p.BN); return B200LORA_E_SHAPE; }
+  p.scale = scale;
+  p.S1 = S1; p.s1_rs = s1_rs; p.s1_cs = s1_cs;
+  p.S2 = S2; p.s2_rs = s2_rs; p.s2_cs = s2_cs;
+  p.ab_dtype = ab_dtype; p.bias = bias; p.bias_dtype = bias_dtype; p.T_out = T_out;
+  const unsigned fmt = io_dtype == B200LORA_BF16 ? 1u : 0u;
+  // kind::f16 idesc: D=f32 (1<<4), A/B format, N>>3 at bit 17, M>>4 at bit 24
+  p.idesc_main = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)(p.BN + 16) >> 3) << 17) | ((128u >> 4) << 24);
+  p.idesc_tail = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)p.BN >> 3) << 17) | ((128u >> 4) << 24);
+
+  CUtensorMap tmX, tmW, tmY;
+  int rc;
+  if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmW, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)p.BN, 64,
+                     io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  DevInfo di = dev_info();
+  cudaError_t e = io_dtype == B200LORA_BF16
+                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmY, p, smem, di.sms, stream)
+                      : launch_tc<__half>(tmX, tmW, tmY, p, smem, di.sms, stream);
+  if (e != cudaSuccess) {
+    set_error("tc launch failed: %s", cudaGetErrorString(e));
+    return B200LORA_E_CUDA;
+  }
+  return 0;
+}
+
+static int run_simt(const void* X, long long ldx, const void* W, long long ldw, int w_layout,
+                    const void* bias, int bias_dtype, const void* S1, long long s1_rs,
+                    long long s1_cs, const void* S2, long long s2_rs, long long s2_cs, int ab_dtype,
+                    float scale, void* Y, long long ldy, void* T_out, long long M, int Kc, int Nout,
+                    int r, int io_dtype, cudaStream_t stream) {
+  if (r > 64) { set_error("simt path supports r <= 64 (got %d)", r); return B200LORA_E_SHAPE; }
+  cudaError_t e;
+#define CALL(T)                                                                                   \
+  launch_simt<T>(X, ldx, W, ldw, w_layout, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs,  \
+                 ab_dtype, scale, Y, ldy, T_out, M, Kc, Nout, r, stream)
+  if (io_dtype == B200LORA_F32) e = CALL(float);
+  else if (io_dtype == B200LORA_F16) e = CALL(__half);
+  else e = CALL(__nv_bfloat16);
+#undef CALL
+  if (e != cudaSuccess) { set_error("simt launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+}  // namespace b200
+
+// =========================================================================================
+// extern "C" surface
+// =========================================================================================
+using namespace b200;
+
+static bool valid_dtype(int dt) { return dt == B200LORA_F32 || dt == B200LORA_F16 || dt == B200LORA_BF16; }
+
+extern "C" int b200lora_version(void) { return 100; }
+extern "C" const char* b200lora_last_error(void) { return g_err; }
+extern "C" int b200lora_tc_supported(void) {
+  DevInfo di = dev_info();
+  return di.ok && di.major == 10 ? 1 : 0;
+}
+// diagnostic: non-zero if the tensor-core kernel's watchdog fired (site<<16 | block)
+extern "C" unsigned int b200lora_watchdog_code(void) { return tc_read_watchdog(); }
+
+extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int64_t ldw,
+                                  int w_layout, const void* bias, int bias_dtype, const void* S1,
+                                  int64_t s1_rs, int64_t s1_cs, const void* S2, int64_t s2_rs,
+                                  int64_t s2_cs, int ab_dtype, float scale, void* Y, int64_t ldy,
+                                  void* T_out, int64_t M, int Kc, int Nout, int r, int io_dtype,
+                                  int impl, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!X || !W || !S1 || !S2 || !Y) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(io_dtype) || !valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype))) {
+    set_error("bad dtype enum"); return B200LORA_E_DTYPE;
+  }
+  if (w_layout != B200LORA_W_NK && w_layout != B200LORA_W_KN) { set_error("bad w_layout"); return B200LORA_E_ARG; }
+  if (M < 0 || Kc < 1 || Nout < 1 || r < 1) { set_error("bad shape M=%lld Kc=%d Nout=%d r=%d", (long long)M, Kc, Nout, r); return B200LORA_E_SHAPE; }
+  if (M == 0) return 0;
+  if (ldx < Kc || ldy < Nout || ldw < (w_layout == B200LORA_W_NK ? Kc : Nout)) {
+    set_error("leading dimension smaller than the row length"); return B200LORA_E_SHAPE;
+  }
+  if (impl == B200LORA_IMPL_TC || impl == B200LORA_IMPL_AUTO) {
+    const bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype);
+    if (ok)
+      return run_tc(X, ldx, W, ldw, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs, ab_dtype,
+                    scale, Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
+    if (impl == B200LORA_IMPL_TC) {
+      if (io_dtype == B200LORA_F32) return B200LORA_E_DTYPE;
+      DevInfo di = dev_info();
+      if (!di.ok || di.major != 10) return B200LORA_E_ARCH;
+      return (r > 16 || w_layout != B200LORA_W_NK) ? B200LORA_E_SHAPE : B200LORA_E_ALIGN;
+    }
+    g_err[0] = 0;
+  }
+  return run_simt(X, ldx, W, ldw, w_layout, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs,
+                  ab_dtype, scale, Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
+}
+
+extern "C" int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
+                                   const void* A, const void* B, int ab_dtype, float scale, void* Y,
+                                   void* T_out, int64_t M, int K, int N, int r, int io_dtype,
+                                   int impl, b200lora_stream_t stream) {
+  // S1 = A [r,K] (row stride K), S2 = B [N,r] (row stride r)
+  return b200lora_lora_gemm(X, K, W0, K, B200LORA_W_NK, bias, bias_dtype, A, K, 1, B, r, 1,
+                            ab_dtype, scale, Y, N, T_out, M, K, N, r, io_dtype, impl, stream);
+}
+
+extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout, const void* A,
+                                      const void* B, int ab_dtype, float scale, void* dX,
+                                      void* dT_out, int64_t M, int K, int N, int r, int io_dtype,
+                                      int impl, b200lora_stream_t stream) {
+  // dX = dY·W0 + (s·dY·B)·A : contraction over N.  S1 = Bᵀ (logical [r,N]: (j,n) -> B[n*r+j]),
+  // S2 = Aᵀ (logical [K,r]: (k,j) -> A[j*K+k]).  W as [K,N] (NK layout of the transposed
+  // problem) or W0 itself [N,K] (KN layout).
+  const int64_t ldw = (w_layout == B200LORA_W_NK) ? N : K;
+  return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, A, 1, K, ab_dtype, scale,
+                            dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+}
+
+extern "C" int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r) {
+  const int RP = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  // worst case over element sizes (fp32 has the narrowest column tile -> most column blocks,
+  // 16-bit the most splits); take the max of both
+  int64_t best = 0;
+  for (int es = 2; es <= 4; es += 2) {
+    const int64_t a = (int64_t)grad_reduce_splits(M, K, es) * K * RP * 4;
+    const int64_t b = (int64_t)grad_reduce_splits(M, N, es) * N * RP * 4;
+    if (a + b > best) best = a + b;
+  }
+  return best + 256;
+}
+
+extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T, const void* dT,
+                                   float scale, float* dA, float* dB, int64_t M, int K, int N,
+                                   int r, int io_dtype, int deterministic, void* workspace,
+                                   int64_t workspace_bytes, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (r < 1 || r > 16) { set_error("lora_grads supports 1 <= r <= 16 (got %d)", r); return B200LORA_E_SHAPE; }
+  if (M <= 0) return 0;
+  const int vec = 16 / dtype_size(io_dtype);
+  if ((dB && (N % vec)) || (dA && (K % vec))) { set_error("lora_grads needs N and K multiples of %d", vec); return B200LORA_E_ALIGN; }
+  if ((dB && (!dY || !T)) || (dA && (!X || !dT))) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  float* partA = nullptr;
+  float* partB = nullptr;
+  if (deterministic) {
+    if (!workspace || workspace_bytes < b200lora_lora_grads_workspace(M, K, N, r)) {
+      set_error("deterministic mode needs a workspace of b200lora_lora_grads_workspace bytes");
+      return B200LORA_E_ARG;
+    }
+    const int RP = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+    partA = reinterpret_cast<float*>(workspace);
+    partB = partA + (int64_t)grad_reduce_splits(M, K, dtype_size(io_dtype)) * K * RP;
+  }
+  cudaError_t e = cudaSuccess;
+#define RUN(T_)                                                                                  \
+  do {                                                                                           \
+    if (dB) e = launch_grad_reduce<T_>(dY, N, T, r, scale, dB, /*cs=*/r, /*js=*/1, partB, M, N, stream); \
+    if (e == cudaSuccess && dA)                                                                  \
+      e = launch_grad_reduce<T_>(X, K, dT, r, scale, dA, /*cs=*/1, /*js=*/K, partA, M, K, stream); \
+  } while (0)
+  if (io_dtype == B200LORA_F32) RUN(float);
+  else if (io_dtype == B200LORA_F16) RUN(__half);
+  else RUN(__nv_bfloat16);
+#undef RUN
+  if (e != cudaSuccess) { set_error("lora_grads launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_merge(const void* Win, void* Wout, const void* up, const void* down,
+                              float alpha, int N, int K, int r, int w_dtype, int lora_dtype,
+                              b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!Win || !Wout || !up || !down) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(w_dtype) || !valid_dtype(lora_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (N < 1 || K < 1 || r < 1) { set_error("bad shape"); return B200LORA_E_SHAPE; }
+  const int vec = 16 / dtype_size(w_dtype);
+  if (K % vec || !aligned16(Win) || !aligned16(Wout)) { set_error("merge needs K %% %d == 0 and 16-byte aligned W", vec); return B200LORA_E_ALIGN; }
+  cudaError_t e;
+#define M2(TW, TL) launch_merge<TW, TL, 0>(Win, Wout, up, down, alpha, N, K, r, nullptr, stream)
+#define M1(TW)                                                          \
+  (lora_dtype == B200LORA_F32 ? M2(TW, float)                           \
+   : lora_dtype == B200LORA_F16 ? M2(TW, __half) : M2(TW, __nv_bfloat16))
+  if (w_dtype == B200LORA_F32) e = M1(float);
+  else if (w_dtype == B200LORA_F16) e = M1(__half);
+  else e = M1(__nv_bfloat16);
+#undef M1
+#undef M2
+  if (e != cudaSuccess) { set_error("merge launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_absmean_accum(const void* up, const void* down, float* out_sum, int N,
+                                      int K, int r, int lora_dtype, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!up || !down || !out_sum) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(lora_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (r < 1 || r > 16) { set_error("absmean supports 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  const int vec = 16 / dtype_size(lora_dtype);
+  if (K % vec) { set_error("absmean needs K %% %d == 0", vec); return B200LORA_E_ALIGN; }
+  cudaError_t e;
+  if (lora_dtype == B200LORA_F32) e = launch_merge<float, float, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
+  else if (lora_dtype == B200LORA_F16) e = launch_merge<__half, __half, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
+  else e = launch_merge<__nv_bfloat16, __nv_bfloat16, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
+  if (e != cudaSuccess) { set_error("absmean launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_svd_epilogue(float* U, const float* S, float* Vh, float hi, int do_scale,
+                                     int N, int K, int r, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!U || !Vh || (do_scale && !S)) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  cudaError_t e = launch_svd_epilogue(U, S, Vh, hi, do_scale, N, K, r, stream);
+  if (e != cudaSuccess) { set_error("svd_epilogue launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}

@@ -1,0 +1,56 @@
+// Shared helpers for all b200lora translation units.
+#pragma once
+#include <cuda.h>  // CUtensorMap (types only; the driver entry point is resolved at run time)
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../../include/b200lora.h"
+
+namespace b200 {
+
+__host__ __device__ inline int dtype_size(int dt) { return dt == B200LORA_F32 ? 4 : 2; }
+
+// generic scalar load of element `idx` of an array of runtime dtype, widened to fp32
+__device__ __forceinline__ float load_as_float(const void* p, int dt, long long idx) {
+  if (dt == B200LORA_F32) return __ldg(reinterpret_cast<const float*>(p) + idx);
+  if (dt == B200LORA_BF16)
+    return __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(p) + idx));
+  return __half2float(__ldg(reinterpret_cast<const __half*>(p) + idx));
+}
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) {
+  return __bfloat162float(v);
+}
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) {
+  return __float2half_rn(v);
+}
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+
+// parameters of the tcgen05 fused GEMM (linear_tc.cu), filled by api.cu
+struct TcParams {
+  long long M;
+  int Kc, Nout, r, BN;
+  int num_m_blk, num_n_blk, num_k_blk, stages;
+  float scale;
+  const void* S1; long long s1_rs, s1_cs;
+  const void* S2; long long s2_rs, s2_cs;
+  int ab_dtype;
+  const void* bias; int bias_dtype;
+  void* T_out;
+  unsigned idesc_main, idesc_tail;
+};
+
+// ---- error plumbing (api.cu owns the storage) ----
+void set_error(const char* fmt, ...);
+
+}  // namespace b200

@@ -1,0 +1,158 @@
+// Bandwidth-bound utility kernels around the LoRA weights:
+//   merge        W <- W + alpha * (up @ down)            (lora.py:423, cli_lora_add.py:78)
+//   absmean      Σ |up @ down|                            (lora.py:744-746, inspect_lora)
+//   svd epilogue U <- clamp(U·diag(S)), Vh <- clamp(Vh)   (cli_svd.py:73-84)
+// Each thread owns one 16-byte vector of a W row; the r x VEC slice of `down` it needs stays
+// in registers while it walks down a strip of rows, so per 16 B of W moved it issues one
+// 16 B load, one 16 B store and one broadcast load of up[n, 0:r].
+#include "common.cuh"
+
+namespace b200 {
+
+namespace mrg {
+constexpr int NT = 256;
+constexpr int ROWS_PER_BLOCK = 32;
+constexpr int MAXR = 64;
+}
+
+// rounding of the rank-r product follows the reference: (up @ down) is produced in the LoRA
+// dtype, cast to the weight dtype, scaled by alpha (rounded), then added (rounded).
+template <typename TW, typename TL>
+__device__ __forceinline__ float merged_value(float w, float p, float alpha) {
+  const float p_l = to_f32(from_f32<TL>(p));          // product rounded to LoRA dtype
+  const float p_w = to_f32(from_f32<TW>(p_l));        // .type(weight.dtype)
+  const float ap = to_f32(from_f32<TW>(__fmul_rn(alpha, p_w)));
+  return __fadd_rn(w, ap);
+}
+
+template <typename TW, typename TL, int MODE>  // MODE 0 = merge, 1 = abs-sum
+__global__ void __launch_bounds__(mrg::NT)
+lora_merge_kernel(const TW* __restrict__ Win, TW* __restrict__ Wout, const TL* __restrict__ up,
+                  const TL* __restrict__ down, float alpha, int N, int K, int r,
+                  float* __restrict__ abs_sum) {
+  constexpr int VEC = 16 / sizeof(TW);
+  const int kv = blockIdx.x * mrg::NT + threadIdx.x;  // vector index along K
+  const int k0 = kv * VEC;
+  const int n_begin = blockIdx.y * mrg::ROWS_PER_BLOCK;
+  int n_end = n_begin + mrg::ROWS_PER_BLOCK;
+  if (n_end > N) n_end = N;
+  float local = 0.f;
+  if (k0 < K) {
+    // K % VEC == 0 guaranteed by the host for the vector path
+    for (int j0 = 0; j0 < r || j0 == 0; j0 += 16) {
+      float d[16][VEC];
+      const int jn = (r - j0) < 16 ? (r - j0) : 16;
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+#pragma unroll
+        for (int v = 0; v < VEC; ++v)
+          d[j][v] = (j < jn) ? to_f32(down[(long long)(j0 + j) * K + k0 + v]) : 0.f;
+      const bool first = (j0 == 0), last = (j0 + 16 >= r);
+      // r <= 16 (the common case) makes exactly one pass; larger r accumulates through Wout
+      for (int n = n_begin; n < n_end; ++n) {
+        float pacc[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) pacc[v] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          if (j < jn) {
+            const float u = to_f32(up[(long long)n * r + j0 + j]);
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) pacc[v] = fmaf(u, d[j][v], pacc[v]);
+          }
+        }
+        if (MODE == 0) {
+          const TW* src = (first ? Win : Wout) + (long long)n * K + k0;
+          uint4 raw = *reinterpret_cast<const uint4*>(src);
+          TW* wv = reinterpret_cast<TW*>(&raw);
+          if (first && last) {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v)
+              wv[v] = from_f32<TW>(merged_value<TW, TL>(to_f32(wv[v]), pacc[v], alpha));
+          } else {  // r > 16: plain fp32 accumulation of alpha * partial product
+#pragma unroll
+            for (int v = 0; v < VEC; ++v)
+              wv[v] = from_f32<TW>(fmaf(alpha, pacc[v], to_f32(wv[v])));
+          }
+          *reinterpret_cast<uint4*>(Wout + (long long)n * K + k0) = raw;
+        } else {
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) local += fabsf(pacc[v]);
+        }
+      }
+      if (last) break;
+    }
+  }
+  if (MODE == 1) {
+    // block reduce -> one atomic per block (MODE 1 requires r <= 16, checked on the host)
+    __shared__ float ws[mrg::NT / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = local;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.f;
+      for (int w = 0; w < mrg::NT / 32; ++w) s += ws[w];
+      atomicAdd(abs_sum, s);
+    }
+  }
+}
+
+template <typename TW, typename TL, int MODE>
+cudaError_t launch_merge(const void* Win, void* Wout, const void* up, const void* down,
+                         float alpha, int N, int K, int r, float* abs_sum, cudaStream_t stream) {
+  constexpr int VEC = 16 / sizeof(TW);
+  const int kvecs = K / VEC;
+  dim3 grid((kvecs + mrg::NT - 1) / mrg::NT, (N + mrg::ROWS_PER_BLOCK - 1) / mrg::ROWS_PER_BLOCK);
+  lora_merge_kernel<TW, TL, MODE><<<grid, mrg::NT, 0, stream>>>(
+      (const TW*)Win, (TW*)Wout, (const TL*)up, (const TL*)down, alpha, N, K, r, abs_sum);
+  return cudaGetLastError();
+}
+
+#define INST(TW, TL)                                                                           \
+  template cudaError_t launch_merge<TW, TL, 0>(const void*, void*, const void*, const void*,   \
+                                               float, int, int, int, float*, cudaStream_t);
+INST(float, float) INST(float, __half) INST(float, __nv_bfloat16)
+INST(__half, float) INST(__half, __half) INST(__half, __nv_bfloat16)
+INST(__nv_bfloat16, float) INST(__nv_bfloat16, __half) INST(__nv_bfloat16, __nv_bfloat16)
+#undef INST
+// abs-sum: the "weight" type only sets the vector width; instantiate with TW == TL
+template cudaError_t launch_merge<float, float, 1>(const void*, void*, const void*, const void*,
+                                                   float, int, int, int, float*, cudaStream_t);
+template cudaError_t launch_merge<__half, __half, 1>(const void*, void*, const void*, const void*,
+                                                     float, int, int, int, float*, cudaStream_t);
+template cudaError_t launch_merge<__nv_bfloat16, __nv_bfloat16, 1>(const void*, void*, const void*,
+                                                                   const void*, float, int, int,
+                                                                   int, float*, cudaStream_t);
+
+// ---- SVD epilogue ----
+__global__ void svd_epilogue_kernel(float* __restrict__ U, const float* __restrict__ S,
+                                    float* __restrict__ Vh, float hi, int do_scale, int N, int K,
+                                    int r) {
+  const long long nu = (long long)N * r, nv = (long long)r * K;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nu + nv;
+       i += (long long)gridDim.x * blockDim.x) {
+    if (i < nu) {
+      float v = U[i];
+      if (do_scale) v *= S[i % r];
+      if (hi >= 0.f) v = fminf(fmaxf(v, -hi), hi);
+      U[i] = v;
+    } else {
+      float v = Vh[i - nu];
+      if (hi >= 0.f) v = fminf(fmaxf(v, -hi), hi);
+      Vh[i - nu] = v;
+    }
+  }
+}
+
+cudaError_t launch_svd_epilogue(float* U, const float* S, float* Vh, float hi, int do_scale,
+                                int N, int K, int r, cudaStream_t stream) {
+  const long long total = (long long)N * r + (long long)r * K;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  svd_epilogue_kernel<<<blocks, 256, 0, stream>>>(U, S, Vh, hi, do_scale, N, K, r);
+  return cudaGetLastError();
+}
+
+}  // namespace b200

@@ -1,0 +1,218 @@
+"""Functional layer over the C-ABI: the fused LoRA-linear autograd op, the weight merge,
+the inspect metric and the SVD-distillation epilogue.
+
+Reference semantics being replaced (lora_diffusion/lora.py in the reference):
+  forward   lora.py:49-50   linear(x) + lora_up(lora_down(x)) * scale
+  backward  autograd of the above (dX, dA, dB; W0 is frozen in every reference flow)
+  merge     lora.py:423     weight + alpha * (up @ down).type(weight.dtype)
+  inspect   lora.py:744-746 (ups @ downs).flatten().abs().mean()
+  distill   cli_svd.py:69-84
+"""
+import os
+
+import torch
+
+from . import _native as nat
+
+
+# --------------------------------------------------------------------------------------------
+# frozen-base shadow copies
+# --------------------------------------------------------------------------------------------
+class BaseWeightCache:
+    """Per-module cache of derived copies of the FROZEN base weight W0:
+      ("cast", dtype)   W0 cast to the compute dtype (autocast with fp32 masters: the reference
+                        re-casts the frozen weight on every call)
+      ("t", dtype)      W0ᵀ [K,N] contiguous in the compute dtype (B operand of the dX GEMM)
+    Entries are keyed on (data_ptr, _version, shape, dtype, device) of the source Parameter, so
+    re-assigning `linear.weight` (weight_apply_lora, monkeypatch_*) or an in-place update through
+    autograd-visible ops invalidates them.  In-place edits through `.data` do not bump
+    `_version`; call `invalidate()` after such an edit.
+    """
+
+    def __init__(self):
+        self._store = {}
+
+    @staticmethod
+    def _key(w):
+        return (w.data_ptr(), w._version, tuple(w.shape), w.dtype, w.device)
+
+    def get(self, w, kind, dtype):
+        slot = (kind, dtype)
+        key = self._key(w)
+        hit = self._store.get(slot)
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        with torch.no_grad():
+            base = w.detach()
+            if kind == "cast":
+                out = base.to(dtype).contiguous()
+            elif kind == "t":
+                out = base.to(dtype).t().contiguous()
+            else:
+                raise KeyError(kind)
+        self._store[slot] = (key, out)
+        return out
+
+    def invalidate(self):
+        self._store.clear()
+
+
+def _impl_from_env():
+    v = os.environ.get("B200LORA_IMPL", "auto").lower()
+    return {"auto": nat.IMPL_AUTO, "simt": nat.IMPL_SIMT, "tc": nat.IMPL_TC}.get(v, nat.IMPL_AUTO)
+
+
+_CC_CACHE = {}
+
+
+def _is_sm100(device):
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _CC_CACHE:
+        _CC_CACHE[idx] = torch.cuda.get_device_capability(idx)[0] == 10
+    return _CC_CACHE[idx]
+
+
+def _tc_ok(cdt, K, N, r, device, impl):
+    """Mirror of tc_applicable() in csrc/api.cu (decides which layout of W0 the dX call gets)."""
+    if impl == nat.IMPL_SIMT:
+        return False
+    return cdt in (torch.bfloat16, torch.float16) and 1 <= r <= 16 and K % 8 == 0 and N % 8 == 0 \
+        and _is_sm100(device)
+
+
+def _compute_dtype(x, w0):
+    if torch.is_autocast_enabled("cuda"):
+        return torch.get_autocast_dtype("cuda")
+    if x.dtype != w0.dtype:
+        raise RuntimeError(
+            f"LoraInjectedLinear: input dtype {x.dtype} and weight dtype {w0.dtype} differ "
+            "(outside autocast the reference's F.linear raises here too)")
+    return x.dtype
+
+
+class _LoraLinearFn(torch.autograd.Function):
+    """y = x·W0ᵀ + b + s·(x·Aᵀ)·Bᵀ as ONE kernel; backward = fused dX kernel + token reductions."""
+
+    @staticmethod
+    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic):
+        nat.require_cuda(x, "LoraInjectedLinear.forward")
+        for name, t in (("linear.weight", w0), ("lora_down.weight", A), ("lora_up.weight", B)):
+            if t.device != x.device:
+                raise RuntimeError(f"{name} is on {t.device} but the input is on {x.device}")
+        lib = nat.lib()
+        cdt = _compute_dtype(x, w0)
+        N, K = w0.shape
+        r = A.shape[0]
+        if A.shape != (r, K) or B.shape != (N, r):
+            raise RuntimeError(f"LoRA shapes do not match the base: down {tuple(A.shape)}, "
+                               f"up {tuple(B.shape)}, base {(N, K)}")
+        if x.shape[-1] != K:
+            raise RuntimeError(f"input feature size {x.shape[-1]} != in_features {K}")
+        if A.dtype != B.dtype:
+            raise RuntimeError("lora_down and lora_up must share a dtype")
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, K)
+        if x2.dtype != cdt:
+            x2 = x2.to(cdt)
+        x2 = x2.contiguous()
+        M = x2.shape[0]
+        if cache is None:
+            cache = BaseWeightCache()
+        w = w0.detach() if (w0.dtype == cdt and w0.is_contiguous()) else cache.get(w0, "cast", cdt)
+        Ac = A.detach().contiguous()
+        Bc = B.detach().contiguous()
+        bc = bias.detach().contiguous() if bias is not None else None
+        use_tc = _tc_ok(cdt, K, N, r, x.device, impl)
+        need_grad = any(ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
+        y = torch.empty((M, N), dtype=cdt, device=x.device)
+        T = torch.empty((M, r), dtype=cdt, device=x.device) if need_grad else None
+        if M > 0:
+            with torch.cuda.device(x.device):
+                rc = lib.b200lora_linear_fwd(
+                    nat.ptr(x2), nat.ptr(w), nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
+                    nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype), float(scale),
+                    nat.ptr(y), nat.ptr(T), M, K, N, r, nat.dtype_code(cdt),
+                    nat.IMPL_TC if use_tc else nat.IMPL_SIMT, nat.stream_ptr(x.device))
+            nat.check(rc, "b200lora_linear_fwd")
+        if need_grad:
+            ctx.save_for_backward(x2, T, A, B, w0, w)
+            ctx.meta = (lead, M, K, N, r, float(scale), cdt, use_tc, cache, bool(deterministic),
+                        x.dtype, bias is not None)
+        return y.reshape(*lead, N)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dy):
+        x2, T, A, B, w0, w = ctx.saved_tensors
+        lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias = ctx.meta
+        lib = nat.lib()
+        dev = dy.device
+        dy2 = dy.reshape(-1, N)
+        if dy2.dtype != cdt:
+            dy2 = dy2.to(cdt)
+        dy2 = dy2.contiguous()
+        need_x, need_w, need_b, need_A, need_B = ctx.needs_input_grad[:5]
+        Ac = A.detach().contiguous()
+        Bc = B.detach().contiguous()
+        ab_code = nat.dtype_code(Ac.dtype)
+        io_code = nat.dtype_code(cdt)
+        dx = None
+        dT = None
+        stream = nat.stream_ptr(dev)
+        with torch.cuda.device(dev):
+            if (need_x or need_A) and M > 0:
+                # dX = dY·W0 + s·(dY·B)·A and dT = dY·B in one kernel.  When only dA is needed
+                # (frozen input, e.g. attn2.to_k on the text context) dX is still produced: dT
+                # falls out of the same pass.
+                dx = torch.empty((M, K), dtype=cdt, device=dev)
+                dT = torch.empty((M, r), dtype=cdt, device=dev)
+                if use_tc:
+                    wt = cache.get(w0, "t", cdt)
+                    rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(wt), nat.W_NK, nat.ptr(Ac),
+                                                    nat.ptr(Bc), ab_code, scale, nat.ptr(dx),
+                                                    nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_TC, stream)
+                else:
+                    rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(w), nat.W_KN, nat.ptr(Ac),
+                                                    nat.ptr(Bc), ab_code, scale, nat.ptr(dx),
+                                                    nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_SIMT, stream)
+                nat.check(rc, "b200lora_linear_bwd_dx")
+            dA = dB = None
+            if (need_A or need_B):
+                dA32 = torch.zeros((r, K), dtype=torch.float32, device=dev) if need_A else None
+                dB32 = torch.zeros((N, r), dtype=torch.float32, device=dev) if need_B else None
+                if M > 0:
+                    ws = None
+                    ws_bytes = 0
+                    if deterministic:
+                        ws_bytes = int(lib.b200lora_lora_grads_workspace(M, K, N, r))
+                        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+                    rc = lib.b200lora_lora_grads(nat.ptr(dy2), nat.ptr(x2), nat.ptr(T), nat.ptr(dT),
+                                                 scale, nat.ptr(dA32), nat.ptr(dB32), M, K, N, r,
+                                                 io_code, 1 if deterministic else 0, nat.ptr(ws),
+                                                 ws_bytes, stream)
+                    nat.check(rc, "b200lora_lora_grads")
+                dA = dA32.to(A.dtype) if need_A else None
+                dB = dB32.to(B.dtype) if need_B else None
+        dW = db = None
+        if need_w:
+            # Unfrozen base: never the case in the reference's flows (unet.requires_grad_(False),
+            # train_lora_dreambooth.py:595).  Served by a library GEMM, not a hot-path kernel.
+            dW = (dy2.t() @ x2).to(w0.dtype)
+        if need_b and has_bias:
+            db = dy2.sum(0)
+        if dx is not None and need_x:
+            dx = dx.reshape(*lead, K)
+            if dx.dtype != x_dtype:
+                dx = dx.to(x_dtype)
+        else:
+            dx = None
+        return dx, dW, db, dA, dB, None, None, None, None
+
+
+def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None):
+    """Functional form of LoraInjectedLinear.forward (reference lora.py:49-50)."""
+    if impl is None:
+        impl = _impl_from_env()
+    if deterministic is None:
+        deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
+    return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic)

@@ -1,0 +1,160 @@
+/*
+ * b200lora.h — C-ABI of the B200-native LoRA-adapted-layer hot path.
+ *
+ * This is the drop-in boundary one layer below the reference's Python API
+ * (the reference, lora_diffusion/lora.py, has no FFI of its own: its "operator
+ * interface" is the nn.Module LoraInjectedLinear, lora.py:32-50).  Every entry
+ * point below names the reference code it replaces.
+ *
+ * Conventions
+ *   - all functions are extern "C", return 0 on success or a negative
+ *     B200LORA_E_* code, never throw, never allocate or free caller memory;
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - matrices are row-major; "ld" arguments are leading dimensions in ELEMENTS;
+ *   - every launch goes to the caller's stream (pass the torch current stream);
+ *   - functions are re-entrant; the only internal mutable state is a mutex-guarded
+ *     cache of TMA descriptors keyed on (pointer, shape, box).
+ *
+ * Notation: X [M,K], W0 [N,K], bias [N], A = lora_down.weight [r,K],
+ * B = lora_up.weight [N,r], s = scale, T = X·Aᵀ [M,r], Y [M,N].
+ */
+#ifndef B200LORA_H_
+#define B200LORA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* opaque: a cudaStream_t passed through as void* so this header needs no CUDA includes */
+typedef void* b200lora_stream_t;
+
+enum {
+  B200LORA_OK = 0,
+  B200LORA_E_ARCH = -1,   /* device is not sm_100 (tensor-core path) / no device     */
+  B200LORA_E_SHAPE = -2,  /* unsupported / inconsistent shape                         */
+  B200LORA_E_ALIGN = -3,  /* pointer or leading dimension not aligned for this path   */
+  B200LORA_E_DTYPE = -4,  /* unsupported dtype combination                            */
+  B200LORA_E_CUDA = -5,   /* a CUDA runtime/driver call failed (see last_error)       */
+  B200LORA_E_ARG = -6     /* null pointer / bad enum                                  */
+};
+
+/* element types */
+enum { B200LORA_F32 = 0, B200LORA_F16 = 1, B200LORA_BF16 = 2 };
+
+/* kernel family selection */
+enum {
+  B200LORA_IMPL_AUTO = 0, /* tcgen05 for 16-bit io when shape/alignment allow, else SIMT */
+  B200LORA_IMPL_SIMT = 1, /* CUDA-core FFMA kernels (true-fp32 accumulate; fp32 mode)  */
+  B200LORA_IMPL_TC = 2    /* tcgen05/TMEM/TMA kernel; error if not applicable          */
+};
+
+/* layout of the big frozen operand handed to b200lora_lora_gemm */
+enum {
+  B200LORA_W_NK = 0, /* W given as [Nout, Kc] (contraction index contiguous)  */
+  B200LORA_W_KN = 1  /* W given as [Kc, Nout] (output index contiguous)       */
+};
+
+int b200lora_version(void);
+/* human-readable text of the last failure on the calling thread ("" if none) */
+const char* b200lora_last_error(void);
+/* 1 if the current device can run the tcgen05 path (compute capability 10.x) */
+int b200lora_tc_supported(void);
+
+/*
+ * The generic fused kernel behind forward and backward-dX:
+ *
+ *     T = X · S1ᵀ                       [M, r]   (optionally written to T_out)
+ *     Y = X · Wᵀ + bias + (s·T) · S2ᵀ   [M, Nout]
+ *
+ * X [M,Kc] (ldx), W per w_layout (ldw), S1 logical [r,Kc] with element (j,k) at
+ * S1[j*s1_rs + k*s1_cs], S2 logical [Nout,r] with element (n,j) at S2[n*s2_rs + j*s2_cs].
+ * io_dtype is the type of X, W, Y and T_out; ab_dtype the type of S1/S2 (fp32 masters
+ * under autocast are read directly); bias may be NULL.
+ * On the tcgen05 path this is ONE kernel: the rank-r rows ride along as 16 extra
+ * accumulator columns of the same MMA and the up-projection is one more K=16 MMA step
+ * ([X | sT]·[Wᵀ ; S2ᵀ]), so no separate low-rank GEMM or elementwise add runs.
+ */
+int b200lora_lora_gemm(const void* X, int64_t ldx,
+                       const void* W, int64_t ldw, int w_layout,
+                       const void* bias, int bias_dtype,
+                       const void* S1, int64_t s1_rs, int64_t s1_cs,
+                       const void* S2, int64_t s2_rs, int64_t s2_cs, int ab_dtype,
+                       float scale,
+                       void* Y, int64_t ldy,
+                       void* T_out /* nullable, [M,r] compact */,
+                       int64_t M, int Kc, int Nout, int r,
+                       int io_dtype, int impl, b200lora_stream_t stream);
+
+/*
+ * Forward of LoraInjectedLinear — replaces lora.py:49-50
+ *   `self.linear(input) + self.lora_up(self.lora_down(input)) * self.scale`
+ * (3 F.linear + mul + add in the reference; one kernel here).
+ * T_out (nullable) receives T = X·Aᵀ for the backward; pass NULL under no_grad.
+ */
+int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
+                        const void* A, const void* B, int ab_dtype, float scale,
+                        void* Y, void* T_out,
+                        int64_t M, int K, int N, int r,
+                        int io_dtype, int impl, b200lora_stream_t stream);
+
+/*
+ * Backward w.r.t. the input — replaces the autograd of lora.py:50:
+ *   dX = dY·W0 + s·(dY·B)·A ;  dT_out = dY·B  [M,r]
+ * W0 is frozen, so no dW0 is produced.  w_layout says how W is laid out:
+ *   B200LORA_W_NK: W is W0ᵀ stored [K,N] (a cached transpose; required by the tcgen05 path)
+ *   B200LORA_W_KN: W is W0 itself [N,K] (accepted by the SIMT path only)
+ */
+int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout,
+                           const void* A, const void* B, int ab_dtype, float scale,
+                           void* dX, void* dT_out,
+                           int64_t M, int K, int N, int r,
+                           int io_dtype, int impl, b200lora_stream_t stream);
+
+/*
+ * Token reductions for the LoRA gradients — replaces the autograd of lora.py:50:
+ *   dB[n,j] (+)= s · Σ_m dY[m,n]·T[m,j]      [N,r]
+ *   dA[j,k] (+)= s · Σ_m dT[m,j]·X[m,k]      [r,K]
+ * dA/dB are fp32 accumulators (e.g. slices of the flat gradient arena).  The kernel ADDS
+ * into them (zero them first for a plain gradient).  Either of dA/dB may be NULL to skip.
+ * deterministic=1 uses a two-stage reduction through `workspace` (bytes from
+ * b200lora_lora_grads_workspace) instead of fp32 atomics.
+ */
+int b200lora_lora_grads(const void* dY, const void* X, const void* T, const void* dT,
+                        float scale, float* dA, float* dB,
+                        int64_t M, int K, int N, int r, int io_dtype,
+                        int deterministic, void* workspace, int64_t workspace_bytes,
+                        b200lora_stream_t stream);
+int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r);
+
+/*
+ * Weight merge — replaces lora.py:423  `weight + alpha * (up @ down).type(weight.dtype)`
+ * (cli_lora_add.py:78 runs it on the CPU).  Wout may alias Win (in-place).
+ * up [N,r], down [r,K] in lora_dtype; W in w_dtype.  Rounding follows the reference:
+ * the product is rounded to lora_dtype, cast to w_dtype, multiplied by alpha, then added.
+ */
+int b200lora_merge(const void* Win, void* Wout, const void* up, const void* down,
+                   float alpha, int N, int K, int r, int w_dtype, int lora_dtype,
+                   b200lora_stream_t stream);
+
+/*
+ * mean(|up @ down|) for one layer — replaces lora.py:744-746 (inspect_lora "moved" metric).
+ * out_sum receives Σ|up@down| (fp32, ADDED into; divide by N*K on the host).
+ */
+int b200lora_absmean_accum(const void* up, const void* down, float* out_sum,
+                           int N, int K, int r, int lora_dtype, b200lora_stream_t stream);
+
+/*
+ * Epilogue of the SVD distillation — replaces cli_svd.py:73-84: U ← clamp(U·diag(S), ±hi),
+ * Vh ← clamp(Vh, ±hi).  The SVD itself stays on cuSOLVER and the quantile `hi` is computed
+ * by the caller (cli_svd.py:79-80); pass hi<0 to skip clamping (used to build the quantile
+ * input).  U [N,r] fp32 in/out, S [r], Vh [r,K] fp32 in/out.
+ */
+int b200lora_svd_epilogue(float* U, const float* S, float* Vh, float hi, int do_scale,
+                          int N, int K, int r, b200lora_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LORA_H_ */
