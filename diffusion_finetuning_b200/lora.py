@@ -1,0 +1,690 @@
+"""Drop-in host API of the reference's `lora_diffusion/lora.py`, written from scratch on top of
+the B200 kernels.  Same names, argument meaning, return conventions, on-disk formats and error
+behaviour as the reference (file:line citations are into /root/reference/lora_diffusion/lora.py);
+the compute of every injected layer goes through `ops.lora_linear` (one fused sm_100a kernel).
+
+Additions the reference snapshot lacks but BASELINE.json's north_star names:
+`LoraInjectedConv2d`, `inject_trainable_lora_extended`, `dropout_p`, `selector`,
+`set_selector_from_diag`, `realize_as_lora` — specified in SURVEY §8(c); parity for these is
+pinned by our own PyTorch restatement only ("parity unpinned by the reference").
+"""
+import json
+import math
+from itertools import groupby
+from typing import Dict, List, Optional, Set, Tuple, Type, Union
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+try:
+    from safetensors.torch import safe_open
+    from safetensors.torch import save_file as safe_save
+
+    safetensors_available = True
+except ImportError:  # pragma: no cover - safetensors is part of the image
+    safetensors_available = False
+
+    def safe_open(*args, **kwargs):
+        raise EnvironmentError("Reading .safetensors requires the safetensors library.")
+
+    def safe_save(tensors, filename, metadata=None):
+        # same failure mode as the reference's stub (lora.py:19-27)
+        raise EnvironmentError(
+            "Saving safetensors requires the safetensors library. Please install with pip or similar."
+        )
+
+
+# ---------------------------------------------------------------------------------------------
+# injected layers
+# ---------------------------------------------------------------------------------------------
+def _check_rank(r, a, b):
+    if r > min(a, b):
+        # reference lora.py:36-39
+        raise ValueError(f"LoRA rank {r} must be less or equal than {min(a, b)}")
+
+
+class LoraInjectedLinear(nn.Module):
+    """`y = linear(x) + lora_up(selector(lora_down(x))) * scale` (reference lora.py:32-50).
+
+    Attribute contract kept from the reference: sub-modules `.linear`, `.lora_down`, `.lora_up`
+    (plain nn.Linear so state_dict keys, `.weight` re-assignment and `.out_features` reads keep
+    working) and a mutable float `.scale` read at call time.  `dropout_p` / `selector` follow
+    upstream cloneofsimo/lora; `dropout_p` defaults to 0 so the behaviour equals this reference.
+    """
+
+    def __init__(self, in_features, out_features, bias=False, r=4, dropout_p=0.0, scale=1.0):
+        super().__init__()
+        _check_rank(r, in_features, out_features)
+        self.r = r
+        self.linear = nn.Linear(in_features, out_features, bias)
+        self.lora_down = nn.Linear(in_features, r, bias=False)
+        self.dropout = nn.Dropout(dropout_p)
+        self.lora_up = nn.Linear(r, out_features, bias=False)
+        self.scale = scale
+        self.selector = nn.Identity()
+        nn.init.normal_(self.lora_down.weight, std=1 / r)   # lora.py:46
+        nn.init.zeros_(self.lora_up.weight)                 # lora.py:47
+        self._base_cache = ops.BaseWeightCache()
+
+    def _down_weight(self):
+        """lora_down weight with a diagonal selector folded in (selector(T) = T·diag(d))."""
+        A = self.lora_down.weight
+        if isinstance(self.selector, nn.Identity):
+            return A
+        sel = self.selector.weight  # [r, r]
+        return sel.to(A.dtype) @ A
+
+    def forward(self, input):
+        A = self._down_weight()
+        B = self.lora_up.weight
+        if self.training and self.dropout.p > 0.0:
+            # Dropout sits on the branch OUTPUT (upstream placement), which cannot ride inside the
+            # K-concatenated GEMM: run the fused kernel for the base (scale 0 contributes nothing)
+            # and add the dropped branch explicitly.  Parity is graded at dropout = 0.
+            base = ops.lora_linear(input, self.linear.weight, self.linear.bias, A.detach(),
+                                   B.detach(), 0.0, cache=self._base_cache)
+            branch = ops.lora_linear(input, torch.zeros_like(self.linear.weight), None, A, B, 1.0)
+            return base + self.dropout(branch) * self.scale
+        return ops.lora_linear(input, self.linear.weight, self.linear.bias, A, B, self.scale,
+                               cache=self._base_cache)
+
+    def realize_as_lora(self):
+        return self.lora_up.weight.data * self.scale, self.lora_down.weight.data
+
+    def set_selector_from_diag(self, diag: torch.Tensor):
+        assert diag.shape == (self.r,)
+        self.selector = nn.Linear(self.r, self.r, bias=False)
+        self.selector.weight.data = torch.diag(diag)
+        self.selector.weight.data = self.selector.weight.data.to(
+            self.lora_up.weight.device).to(self.lora_up.weight.dtype)
+
+
+class LoraInjectedConv2d(nn.Module):
+    """Conv2d counterpart (absent from the reference snapshot; spec in SURVEY §8(c)):
+    `y = conv(x) + lora_up(selector(lora_down(x))) * scale` with `lora_down` a conv of the same
+    geometry to r channels and `lora_up` a 1x1 conv.
+    """
+
+    def __init__(self, in_channels: int, out_channels: int, kernel_size, stride=1, padding=0,
+                 dilation=1, groups: int = 1, bias: bool = True, r: int = 4,
+                 dropout_p: float = 0.0, scale: float = 1.0):
+        super().__init__()
+        _check_rank(r, in_channels, out_channels)
+        self.r = r
+        self.conv = nn.Conv2d(in_channels, out_channels, kernel_size, stride, padding, dilation,
+                              groups, bias)
+        self.lora_down = nn.Conv2d(in_channels, r, kernel_size, stride, padding, dilation, groups,
+                                   bias=False)
+        self.dropout = nn.Dropout(dropout_p)
+        self.lora_up = nn.Conv2d(r, out_channels, 1, 1, 0, bias=False)
+        self.selector = nn.Identity()
+        self.scale = scale
+        nn.init.normal_(self.lora_down.weight, std=1 / r)
+        nn.init.zeros_(self.lora_up.weight)
+        self._base_cache = ops.BaseWeightCache()
+
+    def forward(self, input):
+        from . import conv_ops  # implicit-GEMM path; imported lazily (K4)
+        return conv_ops.lora_conv2d(self, input)
+
+    def realize_as_lora(self):
+        return self.lora_up.weight.data * self.scale, self.lora_down.weight.data
+
+    def set_selector_from_diag(self, diag: torch.Tensor):
+        assert diag.shape == (self.r,)
+        self.selector = nn.Conv2d(self.r, self.r, 1, 1, 0, bias=False)
+        self.selector.weight.data = torch.diag(diag).reshape(self.r, self.r, 1, 1)
+        self.selector.weight.data = self.selector.weight.data.to(
+            self.lora_up.weight.device).to(self.lora_up.weight.dtype)
+
+
+UNET_DEFAULT_TARGET_REPLACE = {"CrossAttention", "Attention", "GEGLU"}
+UNET_EXTENDED_TARGET_REPLACE = {"ResnetBlock2D", "CrossAttention", "Attention", "GEGLU"}
+TEXT_ENCODER_DEFAULT_TARGET_REPLACE = {"CLIPAttention"}
+TEXT_ENCODER_EXTENDED_TARGET_REPLACE = {"CLIPAttention"}
+DEFAULT_TARGET_REPLACE = UNET_DEFAULT_TARGET_REPLACE
+EMBED_FLAG = "<embed>"
+
+_INJECTED = (LoraInjectedLinear, LoraInjectedConv2d)
+
+
+# ---------------------------------------------------------------------------------------------
+# module discovery (order of yield defines the on-disk order of every saved LoRA)
+# ---------------------------------------------------------------------------------------------
+def _is_any(module, classes):
+    return any(isinstance(module, c) for c in classes)
+
+
+def _find_children(model, search_class: List[Type[nn.Module]] = [nn.Linear]):
+    """(parent, name, child) for every direct child of any module that is an instance of one of
+    `search_class` (reference lora.py:61-75)."""
+    for parent in model.modules():
+        for name, child in parent.named_children():
+            if _is_any(child, search_class):
+                yield parent, name, child
+
+
+def _find_modules_v2(model, ancestor_class: Optional[Set[str]] = None,
+                     search_class: List[Type[nn.Module]] = [nn.Linear],
+                     exclude_children_of: Optional[List[Type[nn.Module]]] = list(_INJECTED)):
+    """(parent, name, module) for every `search_class` descendant of every module whose CLASS
+    NAME is in `ancestor_class`, skipping children of already-injected layers
+    (reference lora.py:78-114: model.modules() pre-order, then named_modules() pre-order)."""
+    if ancestor_class is None:
+        ancestor_class = DEFAULT_TARGET_REPLACE
+    for ancestor in model.modules():
+        if ancestor.__class__.__name__ not in ancestor_class:
+            continue
+        for fullname, module in ancestor.named_modules():
+            if not _is_any(module, search_class):
+                continue
+            parts = fullname.split(".")
+            parent = ancestor
+            for hop in parts[:-1]:
+                parent = parent.get_submodule(hop)
+            if exclude_children_of and _is_any(parent, exclude_children_of):
+                continue
+            yield parent, parts[-1], module
+
+
+def _find_modules_old(model, ancestor_class: Set[str] = DEFAULT_TARGET_REPLACE,
+                      search_class: List[Type[nn.Module]] = [nn.Linear],
+                      exclude_children_of=None):
+    """Legacy finder kept for API parity (reference lora.py:117-131): exact class match, yields the
+    ancestor (not the direct parent) and the dotted name."""
+    found = []
+    for anc in model.modules():
+        if anc.__class__.__name__ in ancestor_class:
+            for name, child in anc.named_modules():
+                if child.__class__ in search_class:
+                    found.append((anc, name, child))
+    print(found)
+    return found
+
+
+_find_modules = _find_modules_v2
+
+
+def _adopt_base(new_layer, old, attr):
+    """Make `new_layer.<attr>` share the ORIGINAL Parameter objects (reference lora.py:164-166)."""
+    inner = getattr(new_layer, attr)
+    inner.weight = old.weight
+    if old.bias is not None:
+        inner.bias = old.bias
+
+
+def _wrap_linear(src: nn.Linear, r, dropout_p=0.0, scale=1.0):
+    layer = LoraInjectedLinear(src.in_features, src.out_features, src.bias is not None, r=r,
+                               dropout_p=dropout_p, scale=scale)
+    _adopt_base(layer, src, "linear")
+    return layer
+
+
+def _wrap_conv(src: nn.Conv2d, r, dropout_p=0.0, scale=1.0):
+    layer = LoraInjectedConv2d(src.in_channels, src.out_channels, src.kernel_size, src.stride,
+                               src.padding, src.dilation, src.groups, src.bias is not None, r=r,
+                               dropout_p=dropout_p, scale=scale)
+    _adopt_base(layer, src, "conv")
+    return layer
+
+
+def _as_param(t):
+    # The reference assigns the popped tensor directly (lora.py:176-177), which only works when
+    # the list holds nn.Parameters; a plain tensor from `save_lora_weight` is wrapped here.
+    return t if isinstance(t, nn.Parameter) else nn.Parameter(t)
+
+
+def _inject(model, targets, search, r, loras, dropout_p, scale):
+    params, names = [], []
+    if loras is not None:
+        loras = torch.load(loras)
+    for parent, name, child in _find_modules(model, targets, search_class=search):
+        layer = _wrap_conv(child, r, dropout_p, scale) if isinstance(child, nn.Conv2d) \
+            else _wrap_linear(child, r, dropout_p, scale)
+        layer.to(child.weight.device).to(child.weight.dtype)     # lora.py:169
+        parent._modules[name] = layer                            # lora.py:170
+        # generators, up first then down — callers do itertools.chain(*params) (lora.py:172-173)
+        params.append(layer.lora_up.parameters())
+        params.append(layer.lora_down.parameters())
+        if loras is not None:                                    # resume: pop up, pop down
+            layer.lora_up.weight = _as_param(loras.pop(0))
+            layer.lora_down.weight = _as_param(loras.pop(0))
+        layer.lora_up.weight.requires_grad = True
+        layer.lora_down.weight.requires_grad = True
+        names.append(name)
+    return params, names
+
+
+def inject_trainable_lora(model: nn.Module, target_replace_module: Set[str] = DEFAULT_TARGET_REPLACE,
+                          r: int = 4, loras=None, verbose: bool = False, dropout_p: float = 0.0,
+                          scale: float = 1.0):
+    """Swap every nn.Linear under the target classes for a LoraInjectedLinear sharing the base
+    Parameters; returns ([up params gen, down params gen, ...], names) (reference lora.py:137-183).
+    `loras` is a path to a `.pt` list to resume from."""
+    return _inject(model, target_replace_module, [nn.Linear], r, loras, dropout_p, scale)
+
+
+def inject_trainable_lora_extended(model: nn.Module,
+                                   target_replace_module: Set[str] = UNET_EXTENDED_TARGET_REPLACE,
+                                   r: int = 4, loras=None, dropout_p: float = 0.0, scale: float = 1.0):
+    """As `inject_trainable_lora` but also wraps nn.Conv2d (resnet convs) — SURVEY §8(c) A14."""
+    return _inject(model, target_replace_module, [nn.Linear, nn.Conv2d], r, loras, dropout_p, scale)
+
+
+# ---------------------------------------------------------------------------------------------
+# extract / save / load
+# ---------------------------------------------------------------------------------------------
+def extract_lora_ups_down(model, target_replace_module=DEFAULT_TARGET_REPLACE):
+    """[(lora_up, lora_down) modules] in discovery order (reference lora.py:186-198)."""
+    pairs = [(m.lora_up, m.lora_down)
+             for _, _, m in _find_modules(model, target_replace_module, search_class=list(_INJECTED))]
+    if not pairs:
+        raise ValueError("No lora injected.")
+    return pairs
+
+
+def extract_lora_as_tensor(model, target_replace_module=DEFAULT_TARGET_REPLACE, as_fp16=True):
+    """[(up, down) tensors] with `scale` folded into up (upstream helper)."""
+    out = []
+    for _, _, m in _find_modules(model, target_replace_module, search_class=list(_INJECTED)):
+        up, down = m.realize_as_lora()
+        if as_fp16:
+            up, down = up.to(torch.float16), down.to(torch.float16)
+        out.append((up, down))
+    if not out:
+        raise ValueError("No lora injected.")
+    return out
+
+
+def save_lora_weight(model, path="./lora.pt", target_replace_module=DEFAULT_TARGET_REPLACE):
+    """`.pt` format: flat list [up0, down0, up1, down1, ...] as fp16 on the CPU
+    (reference lora.py:201-213; the fp16 cast is lossy by design)."""
+    flat = []
+    for up, down in extract_lora_ups_down(model, target_replace_module=target_replace_module):
+        flat.append(up.weight.to("cpu").to(torch.float16))
+        flat.append(down.weight.to("cpu").to(torch.float16))
+    torch.save(flat, path)
+
+
+def save_lora_as_json(model, path="./lora.json"):
+    """Nested-list JSON dump (reference lora.py:216-225)."""
+    flat = []
+    for up, down in extract_lora_ups_down(model):
+        flat.append(up.weight.detach().cpu().numpy().tolist())
+        flat.append(down.weight.detach().cpu().numpy().tolist())
+    with open(path, "w") as f:
+        json.dump(flat, f)
+
+
+def save_safeloras_with_embeds(modelmap: Dict[str, Tuple[nn.Module, Set[str]]] = {},
+                               embeds: Dict[str, torch.Tensor] = {},
+                               outpath="./lora.safetensors"):
+    """One safetensors file for several models (reference lora.py:228-258).
+    keys `{name}:{i}:up|down`; metadata `{name}` -> JSON target list, `{name}:{i}:rank` -> str(r),
+    `{token}` -> "<embed>"."""
+    weights, metadata = {}, {}
+    for name, (model, targets) in modelmap.items():
+        metadata[name] = json.dumps(list(targets))
+        for i, (up, down) in enumerate(extract_lora_ups_down(model, targets)):
+            rank = down.out_features if isinstance(down, nn.Linear) else down.out_channels
+            metadata[f"{name}:{i}:rank"] = str(rank)
+            weights[f"{name}:{i}:up"] = up.weight
+            weights[f"{name}:{i}:down"] = down.weight
+    for token, tensor in (embeds or {}).items():
+        metadata[token] = EMBED_FLAG
+        weights[token] = tensor
+    print(f"Saving weights to {outpath}")
+    safe_save(weights, outpath, metadata)
+
+
+def save_safeloras(modelmap: Dict[str, Tuple[nn.Module, Set[str]]] = {}, outpath="./lora.safetensors"):
+    return save_safeloras_with_embeds(modelmap=modelmap, outpath=outpath)
+
+
+def convert_loras_to_safeloras_with_embeds(modelmap: Dict[str, Tuple[str, Set[str], int]] = {},
+                                           embeds: Dict[str, torch.Tensor] = {},
+                                           outpath="./lora.safetensors"):
+    """Pack `.pt` LoRA lists into one safetensors file (reference lora.py:268-303);
+    modelmap = {name: (pt_path, targets, rank)}."""
+    weights, metadata = {}, {}
+    for name, (path, targets, r) in modelmap.items():
+        metadata[name] = json.dumps(list(targets))
+        for pos, weight in enumerate(torch.load(path)):
+            i, is_up = divmod(pos, 2)[0], pos % 2 == 0
+            if is_up:
+                metadata[f"{name}:{i}:rank"] = str(r)
+                weights[f"{name}:{i}:up"] = weight
+            else:
+                weights[f"{name}:{i}:down"] = weight
+    for token, tensor in (embeds or {}).items():
+        metadata[token] = EMBED_FLAG
+        weights[token] = tensor
+    print(f"Saving weights to {outpath}")
+    safe_save(weights, outpath, metadata)
+
+
+def convert_loras_to_safeloras(modelmap: Dict[str, Tuple[str, Set[str], int]] = {},
+                               outpath="./lora.safetensors"):
+    convert_loras_to_safeloras_with_embeds(modelmap=modelmap, outpath=outpath)
+
+
+def parse_safeloras(safeloras) -> Dict[str, Tuple[List[nn.parameter.Parameter], List[int], List[str]]]:
+    """{name: ([up0, down0, ...] as Parameters, [rank...], targets)} from an opened safetensors
+    file (reference lora.py:313-371).  Missing metadata raises ValueError (lora.py:339-342)."""
+    metadata = safeloras.metadata()
+    model_of = lambda key: key.split(":")[0]
+    keys = sorted(safeloras.keys(), key=model_of)   # stable: keeps file order inside a model
+    result = {}
+    for name, group in groupby(keys, model_of):
+        info = metadata.get(name)
+        if not info:
+            raise ValueError(f"Tensor {name} has no metadata - is this a Lora safetensor?")
+        if info == EMBED_FLAG:      # textual-inversion embedding, handled elsewhere
+            continue
+        targets = json.loads(info)
+        group = list(group)
+        ranks = [4] * (len(group) // 2)          # default rank 4 (lora.py:354)
+        weights = [None] * len(group)
+        for key in group:
+            _, idx, direction = key.split(":")
+            idx = int(idx)
+            ranks[idx] = int(metadata[f"{name}:{idx}:rank"])
+            weights[2 * idx + (1 if direction == "down" else 0)] = nn.parameter.Parameter(
+                safeloras.get_tensor(key))
+        result[name] = (weights, ranks, targets)
+    return result
+
+
+def parse_safeloras_embeds(safeloras) -> Dict[str, torch.Tensor]:
+    """{token: embedding} for entries flagged "<embed>" (reference lora.py:374-392)."""
+    metadata = safeloras.metadata()
+    return {key: safeloras.get_tensor(key) for key in safeloras.keys()
+            if metadata.get(key) == EMBED_FLAG}
+
+
+def load_safeloras(path, device="cpu"):
+    return parse_safeloras(safe_open(path, framework="pt", device=device))
+
+
+def load_safeloras_embeds(path, device="cpu"):
+    return parse_safeloras_embeds(safe_open(path, framework="pt", device=device))
+
+
+def load_safeloras_both(path, device="cpu"):
+    f = safe_open(path, framework="pt", device=device)
+    return parse_safeloras(f), parse_safeloras_embeds(f)
+
+
+# ---------------------------------------------------------------------------------------------
+# weight merge
+# ---------------------------------------------------------------------------------------------
+def weight_apply_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE, alpha=1.0):
+    """W <- W + alpha * (up @ down).type(W.dtype) for every targeted nn.Linear
+    (reference lora.py:410-424), on the bandwidth-bound merge kernel.  `loras` is consumed."""
+    for _, _, child in _find_modules(model, target_replace_module, search_class=[nn.Linear]):
+        weight = child.weight
+        up = loras.pop(0).detach().to(weight.device)
+        down = loras.pop(0).detach().to(weight.device)
+        child.weight = nn.Parameter(ops.merge_lora_weight(weight, up, down, alpha))
+
+
+def collapse_lora(model, alpha=1.0):
+    """Fold every injected LoRA into its base weight in place (upstream helper)."""
+    for m in model.modules():
+        if isinstance(m, LoraInjectedLinear):
+            up, down = m.lora_up.weight.data, m.lora_down.weight.data
+            if not isinstance(m.selector, nn.Identity):
+                down = m.selector.weight.data.to(down.dtype) @ down
+            m.linear.weight = nn.Parameter(
+                ops.merge_lora_weight(m.linear.weight, up, down, alpha * m.scale),
+                requires_grad=m.linear.weight.requires_grad)
+
+
+# ---------------------------------------------------------------------------------------------
+# monkeypatch family: load trained up/down weights into a model
+# ---------------------------------------------------------------------------------------------
+def _base_of(module):
+    """The plain nn.Linear / nn.Conv2d behind `module` (unwraps an injected layer)."""
+    if isinstance(module, LoraInjectedLinear):
+        return module.linear
+    if isinstance(module, LoraInjectedConv2d):
+        return module.conv
+    return module
+
+
+def _load_pair(layer, loras, weight):
+    """Pop (up, down) from `loras`, cast to the base weight's dtype, install as fresh Parameters
+    and move the layer to the base weight's device (reference lora.py:449-459)."""
+    up = loras.pop(0)
+    down = loras.pop(0)
+    layer.lora_up.weight = nn.Parameter(up.type(weight.dtype))
+    layer.lora_down.weight = nn.Parameter(down.type(weight.dtype))
+    layer.to(weight.device)
+
+
+def _patch(model, loras, targets, search, r):
+    for parent, name, child in _find_modules(model, targets, search_class=search):
+        src = _base_of(child)
+        rank = r.pop(0) if isinstance(r, list) else r      # per-layer ranks (lora.py:518)
+        layer = _wrap_conv(src, rank) if isinstance(src, nn.Conv2d) else _wrap_linear(src, rank)
+        parent._modules[name] = layer
+        _load_pair(layer, loras, src.weight)
+
+
+def monkeypatch_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE, r: int = 4):
+    """Inject fresh LoRA layers over plain nn.Linear and load `loras` (reference lora.py:427-459)."""
+    _patch(model, loras, target_replace_module, [nn.Linear], r)
+
+
+def monkeypatch_replace_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE, r: int = 4):
+    """Replace the LoRA of already-injected layers (reference lora.py:462-494)."""
+    _patch(model, loras, target_replace_module, [LoraInjectedLinear], r)
+
+
+def monkeypatch_or_replace_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE,
+                                r: Union[int, List[int]] = 4):
+    """Either of the above per layer; `r` may be a list popped per layer
+    (reference lora.py:497-538)."""
+    _patch(model, loras, target_replace_module, [nn.Linear, LoraInjectedLinear], r)
+
+
+def monkeypatch_or_replace_lora_extended(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE,
+                                         r: Union[int, List[int]] = 4):
+    """Linear + Conv2d variant (upstream)."""
+    _patch(model, loras, target_replace_module,
+           [nn.Linear, LoraInjectedLinear, nn.Conv2d, LoraInjectedConv2d], r)
+
+
+def monkeypatch_or_replace_safeloras(models, safeloras):
+    """Patch every model named in an opened safetensors file (reference lora.py:541-551)."""
+    for name, (lora, ranks, target) in parse_safeloras(safeloras).items():
+        model = getattr(models, name, None)
+        if not model:
+            print(f"No model provided for {name}, contained in Lora")
+            continue
+        monkeypatch_or_replace_lora_extended(model, lora, target, ranks)
+
+
+def monkeypatch_remove_lora(model):
+    """Put plain layers back, sharing the base Parameters (reference lora.py:554-567)."""
+    for parent, name, child in _find_children(model, search_class=list(_INJECTED)):
+        src = _base_of(child)
+        if isinstance(src, nn.Conv2d):
+            plain = nn.Conv2d(src.in_channels, src.out_channels, src.kernel_size, src.stride,
+                              src.padding, src.dilation, src.groups, src.bias is not None)
+        else:
+            plain = nn.Linear(src.in_features, src.out_features, src.bias is not None)
+        plain.weight = src.weight
+        if src.bias is not None:
+            plain.bias = src.bias
+        parent._modules[name] = plain
+
+
+def monkeypatch_add_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE,
+                         alpha: float = 1.0, beta: float = 1.0):
+    """up <- alpha*new + beta*old (same for down) on injected layers (reference lora.py:570-594)."""
+    for parent, name, child in _find_modules(model, target_replace_module,
+                                             search_class=[LoraInjectedLinear]):
+        weight = child.linear.weight
+        up = loras.pop(0)
+        down = loras.pop(0)
+        layer = parent._modules[name]
+        layer.lora_up.weight = nn.Parameter(
+            up.type(weight.dtype).to(weight.device) * alpha
+            + layer.lora_up.weight.to(weight.device) * beta)
+        layer.lora_down.weight = nn.Parameter(
+            down.type(weight.dtype).to(weight.device) * alpha
+            + layer.lora_down.weight.to(weight.device) * beta)
+        layer.to(weight.device)
+
+
+def tune_lora_scale(model, alpha: float = 1.0):
+    """Set `.scale` on every injected layer (reference lora.py:597-600; matched by class NAME,
+    and the Conv2d class too as upstream does).  `scale` is a runtime kernel argument."""
+    for m in model.modules():
+        if m.__class__.__name__ in ("LoraInjectedLinear", "LoraInjectedConv2d"):
+            m.scale = alpha
+
+
+def set_lora_diag(model, diag: torch.Tensor):
+    for m in model.modules():
+        if m.__class__.__name__ in ("LoraInjectedLinear", "LoraInjectedConv2d"):
+            m.set_selector_from_diag(diag)
+
+
+def _text_lora_path(path: str) -> str:
+    assert path.endswith(".pt"), "Only .pt files are supported"
+    return ".".join(path.split(".")[:-1] + ["text_encoder", "pt"])
+
+
+def _ti_lora_path(path: str) -> str:
+    assert path.endswith(".pt"), "Only .pt files are supported"
+    return ".".join(path.split(".")[:-1] + ["ti", "pt"])
+
+
+# ---------------------------------------------------------------------------------------------
+# textual-inversion embeddings (host plumbing; not a kernel target — SURVEY §2.1 C8)
+# ---------------------------------------------------------------------------------------------
+def apply_learned_embed_in_clip(learned_embeds, text_encoder, tokenizer,
+                                token: Optional[Union[str, List[str]]] = None, idempotent=False):
+    """Add tokens to the tokenizer, grow the embedding table and write the learned vectors
+    (reference lora.py:613-656)."""
+    if isinstance(token, str):
+        trained_tokens = [token]
+    elif isinstance(token, list):
+        assert len(learned_embeds.keys()) == len(token), \
+            "The number of tokens and the number of embeds should be the same"
+        trained_tokens = token
+    else:
+        trained_tokens = list(learned_embeds.keys())
+    for token in trained_tokens:
+        print(token)
+        embeds = learned_embeds[token]
+        added = tokenizer.add_tokens(token)
+        i = 1
+        if not idempotent:
+            while added == 0:
+                print(f"The tokenizer already contains the token {token}.")
+                token = f"{token[:-1]}-{i}>"
+                print(f"Attempting to add the token {token}.")
+                added = tokenizer.add_tokens(token)
+                i += 1
+        elif added == 0:
+            print(f"The tokenizer already contains the token {token}.")
+            print(f"Replacing {token} embedding.")
+        text_encoder.resize_token_embeddings(len(tokenizer))
+        token_id = tokenizer.convert_tokens_to_ids(token)
+        text_encoder.get_input_embeddings().weight.data[token_id] = embeds
+    return token
+
+
+def load_learned_embed_in_clip(learned_embeds_path, text_encoder, tokenizer,
+                               token: Optional[Union[str, List[str]]] = None, idempotent=False):
+    learned_embeds = torch.load(learned_embeds_path)
+    apply_learned_embed_in_clip(learned_embeds, text_encoder, tokenizer, token, idempotent)
+
+
+def patch_pipe(pipe, maybe_unet_path, token: Optional[str] = None, r: int = 4, patch_unet=True,
+               patch_text=False, patch_ti=False, idempotent_token=True,
+               unet_target_replace_module=DEFAULT_TARGET_REPLACE,
+               text_target_replace_module=TEXT_ENCODER_DEFAULT_TARGET_REPLACE):
+    """Load a `.pt` triple or a `.safetensors` file into a pipeline (reference lora.py:672-732)."""
+    if maybe_unet_path.endswith(".pt"):
+        if maybe_unet_path.endswith(".ti.pt"):
+            unet_path = maybe_unet_path[:-6] + ".pt"
+        elif maybe_unet_path.endswith(".text_encoder.pt"):
+            unet_path = maybe_unet_path[:-16] + ".pt"
+        else:
+            unet_path = maybe_unet_path
+        ti_path = _ti_lora_path(unet_path)
+        text_path = _text_lora_path(unet_path)
+        if patch_unet:
+            print("LoRA : Patching Unet")
+            monkeypatch_or_replace_lora(pipe.unet, torch.load(unet_path), r=r,
+                                        target_replace_module=unet_target_replace_module)
+        if patch_text:
+            print("LoRA : Patching text encoder")
+            monkeypatch_or_replace_lora(pipe.text_encoder, torch.load(text_path),
+                                        target_replace_module=text_target_replace_module, r=r)
+        if patch_ti:
+            print("LoRA : Patching token input")
+            token = load_learned_embed_in_clip(ti_path, pipe.text_encoder, pipe.tokenizer,
+                                               token=token, idempotent=idempotent_token)
+    elif maybe_unet_path.endswith(".safetensors"):
+        safeloras = safe_open(maybe_unet_path, framework="pt", device="cpu")
+        monkeypatch_or_replace_safeloras(pipe, safeloras)
+        tok_dict = parse_safeloras_embeds(safeloras)
+        apply_learned_embed_in_clip(tok_dict, pipe.text_encoder, pipe.tokenizer, token=token,
+                                    idempotent=idempotent_token)
+
+
+@torch.no_grad()
+def inspect_lora(model):
+    """{layer name: [mean |up @ down|]} (reference lora.py:735-752) on the abs-mean kernel."""
+    moved = {}
+    for name, m in model.named_modules():
+        if m.__class__.__name__ in ("LoraInjectedLinear", "LoraInjectedConv2d"):
+            up = m.lora_up.weight.data.flatten(1)
+            down = m.lora_down.weight.data.flatten(1)
+            moved.setdefault(name, []).append(ops.lora_abs_mean(up, down))
+    return moved
+
+
+def save_all(unet, text_encoder, placeholder_token_ids, placeholder_tokens, save_path,
+             save_lora=True, save_ti=True,
+             target_replace_module_text=TEXT_ENCODER_DEFAULT_TARGET_REPLACE,
+             target_replace_module_unet=DEFAULT_TARGET_REPLACE, safe_form=True):
+    """Checkpoint UNet LoRA + text-encoder LoRA + learned embeddings (reference lora.py:755-821)."""
+
+    def learned_rows():
+        rows = {}
+        for tok, tok_id in zip(placeholder_tokens, placeholder_token_ids):
+            vec = text_encoder.get_input_embeddings().weight[tok_id]
+            print(f"Current Learned Embeddings for {tok}:, id {tok_id} ", vec[:4])
+            rows[tok] = vec.detach().cpu()
+        return rows
+
+    if not safe_form:
+        if save_ti:
+            ti_path = _ti_lora_path(save_path)
+            torch.save(learned_rows(), ti_path)
+            print("Ti saved to ", ti_path)
+        if save_lora:
+            save_lora_weight(unet, save_path, target_replace_module=target_replace_module_unet)
+            print("Unet saved to ", save_path)
+            save_lora_weight(text_encoder, _text_lora_path(save_path),
+                             target_replace_module=target_replace_module_text)
+            print("Text Encoder saved to ", _text_lora_path(save_path))
+    else:
+        assert save_path.endswith(".safetensors"), \
+            f"Save path : {save_path} should end with .safetensors"
+        loras = {}
+        embeds = None
+        if save_lora:
+            loras["unet"] = (unet, target_replace_module_unet)
+            loras["text_encoder"] = (text_encoder, target_replace_module_text)
+        if save_ti:
+            embeds = learned_rows()
+        save_safeloras_with_embeds(loras, embeds, save_path)

@@ -216,3 +216,87 @@ def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, d
     if deterministic is None:
         deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
     return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic)
+
+
+# --------------------------------------------------------------------------------------------
+# merge / inspect / distill
+# --------------------------------------------------------------------------------------------
+def _cuda_device():
+    if not torch.cuda.is_available():
+        raise nat.B200LoraError(
+            "no CUDA device: the b200lora kernels are the only compute path (no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def merge_lora_weight(weight, up, down, alpha=1.0):
+    """W + alpha * (up @ down).type(W.dtype)  (reference lora.py:423) on the merge kernel.
+
+    Returns a new tensor with the dtype and device of `weight`.  Host-resident weights (the
+    reference CLI merges on the CPU, cli_lora_add.py:74-78) are staged through the GPU.
+    """
+    lib = nat.lib()
+    home = weight.device
+    dev = home if weight.is_cuda else _cuda_device()
+    with torch.no_grad():
+        w = weight.detach().to(dev).contiguous()
+        u = up.detach().to(dev).contiguous()
+        d = down.detach().to(dev).contiguous()
+        if d.dtype != u.dtype:
+            d = d.to(u.dtype)
+        N, K = w.shape
+        r = u.shape[1]
+        if u.shape != (N, r) or d.shape != (r, K):
+            raise RuntimeError(f"merge: shapes up {tuple(u.shape)} / down {tuple(d.shape)} do not "
+                               f"match weight {(N, K)}")
+        out = torch.empty_like(w)
+        with torch.cuda.device(dev):
+            rc = lib.b200lora_merge(nat.ptr(w), nat.ptr(out), nat.ptr(u), nat.ptr(d), float(alpha),
+                                    N, K, r, nat.dtype_code(w.dtype), nat.dtype_code(u.dtype),
+                                    nat.stream_ptr(dev))
+        nat.check(rc, "b200lora_merge")
+        return out if home == dev else out.to(home)
+
+
+def lora_abs_mean(up, down):
+    """mean(|up @ down|) (reference lora.py:744-746) without materialising the product."""
+    lib = nat.lib()
+    dev = up.device if up.is_cuda else _cuda_device()
+    with torch.no_grad():
+        u = up.detach().to(dev).contiguous()
+        d = down.detach().to(dev).to(u.dtype).contiguous()
+        N, r = u.shape
+        K = d.shape[1]
+        acc = torch.zeros(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.b200lora_absmean_accum(nat.ptr(u), nat.ptr(d), nat.ptr(acc), N, K, r,
+                                            nat.dtype_code(u.dtype), nat.stream_ptr(dev))
+        nat.check(rc, "b200lora_absmean_accum")
+        return acc.item() / float(N * K)
+
+
+def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99):
+    """Rank-r factorisation of one weight difference (reference cli_svd.py:69-84).
+
+    The SVD stays on cuSOLVER (torch.linalg.svd, economy size: only the top-r triplets are kept,
+    so `full_matrices` of the reference is wasted work); U·diag(S), the symmetric clamp at the
+    `clamp_quantile` quantile of [U, Vh] and the slicing run in the epilogue kernel.
+    Returns (U [N,r], Vh [r,K]) fp32 — the `[up, down]` pair the reference saves.
+    """
+    lib = nat.lib()
+    dev = delta.device if delta.is_cuda else _cuda_device()
+    with torch.no_grad():
+        mat = delta.detach().to(dev).float()
+        U, S, Vh = torch.linalg.svd(mat, full_matrices=False)
+        U = U[:, :rank].contiguous()
+        S = S[:rank].contiguous()
+        Vh = Vh[:rank, :].contiguous()
+        N, K = mat.shape
+        stream = nat.stream_ptr(dev)
+        with torch.cuda.device(dev):
+            rc = lib.b200lora_svd_epilogue(nat.ptr(U), nat.ptr(S), nat.ptr(Vh), -1.0, 1, N, K, rank, stream)
+            nat.check(rc, "b200lora_svd_epilogue(scale)")
+            dist = torch.cat([U.flatten(), Vh.flatten()])
+            hi = torch.quantile(dist, clamp_quantile).item()
+            rc = lib.b200lora_svd_epilogue(nat.ptr(U), nat.ptr(S), nat.ptr(Vh), float(hi), 0, N, K, rank, stream)
+            nat.check(rc, "b200lora_svd_epilogue(clamp)")
+        return U, Vh
