@@ -1,0 +1,200 @@
+"""Parity of the CUDA hot path with the oracle, called through the C-ABI (ctypes) and through the
+autograd op.  Tolerances are BASELINE.json's: rel-err <= 1e-5 in fp32, <= 2e-2 in bf16/fp16
+(Frobenius norm of the difference over the norm of the oracle result), dropout = 0."""
+import pytest
+import torch
+
+import diffusion_finetuning_b200 as L
+from conftest import load_golden, rel_err
+from diffusion_finetuning_b200 import _native as nat
+from diffusion_finetuning_b200 import ops
+from oracle import lora_oracle as O
+from oracle.make_golden import LINEAR_CASES
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TOL = {torch.float32: 1e-5, torch.bfloat16: 2e-2, torch.float16: 2e-2}
+
+
+def make_case(M, K, N, r, bias, dtype, seed=0, ab_dtype=None):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(M, K, generator=g)
+    w0 = torch.empty(N, K).uniform_(-K ** -0.5, K ** -0.5, generator=g)
+    b = torch.empty(N).uniform_(-0.1, 0.1, generator=g) if bias else None
+    A = torch.randn(r, K, generator=g) / r
+    B = torch.randn(N, r, generator=g) * 0.02
+    dy = torch.randn(M, N, generator=g)
+    ab = ab_dtype or dtype
+    q = lambda t, dt: None if t is None else t.to(dt)
+    # the oracle sees exactly the values the kernel sees (inputs rounded to the io dtype)
+    host = dict(x=q(x, dtype).float(), w0=q(w0, dtype).float(), b=None if b is None else q(b, dtype).float(),
+                A=q(A, ab).to(dtype).float(), B=q(B, ab).to(dtype).float(), dy=q(dy, dtype).float())
+    dev = dict(x=q(x, dtype).to(DEV), w0=q(w0, dtype).to(DEV), b=None if b is None else q(b, dtype).to(DEV),
+               A=q(A, ab).to(DEV), B=q(B, ab).to(DEV), dy=q(dy, dtype).to(DEV))
+    return host, dev
+
+
+def run_cabi(dev, M, K, N, r, s, dtype, impl):
+    """forward, backward-dX and the gradient reductions straight through the C functions"""
+    lib = nat.lib()
+    io = nat.dtype_code(dtype)
+    ab = nat.dtype_code(dev["A"].dtype)
+    st = nat.stream_ptr(torch.device(DEV))
+    y = torch.empty(M, N, dtype=dtype, device=DEV)
+    T = torch.empty(M, r, dtype=dtype, device=DEV)
+    b = dev["b"]
+    nat.check(lib.b200lora_linear_fwd(nat.ptr(dev["x"]), nat.ptr(dev["w0"]), nat.ptr(b), io, nat.ptr(dev["A"]),
+                                      nat.ptr(dev["B"]), ab, s, nat.ptr(y), nat.ptr(T), M, K, N, r, io, impl, st),
+              "fwd")
+    dx = torch.empty(M, K, dtype=dtype, device=DEV)
+    dT = torch.empty(M, r, dtype=dtype, device=DEV)
+    if impl == nat.IMPL_TC:
+        w = dev["w0"].t().contiguous()
+        lay = nat.W_NK
+    else:
+        w, lay = dev["w0"], nat.W_KN
+    nat.check(lib.b200lora_linear_bwd_dx(nat.ptr(dev["dy"]), nat.ptr(w), lay, nat.ptr(dev["A"]), nat.ptr(dev["B"]),
+                                         ab, s, nat.ptr(dx), nat.ptr(dT), M, K, N, r, io, impl, st), "bwd_dx")
+    dA = torch.zeros(r, K, dtype=torch.float32, device=DEV)
+    dB = torch.zeros(N, r, dtype=torch.float32, device=DEV)
+    nat.check(lib.b200lora_lora_grads(nat.ptr(dev["dy"]), nat.ptr(dev["x"]), nat.ptr(T), nat.ptr(dT), s,
+                                      nat.ptr(dA), nat.ptr(dB), M, K, N, r, io, 0, None, 0, st), "grads")
+    torch.cuda.synchronize()
+    return y, T, dx, dT, dA, dB
+
+
+def check_against_oracle(host, got, s, tol, tag):
+    y, T, dx, dT, dA, dB = got
+    y_ref = O.lora_linear_forward(host["x"], host["w0"], host["b"], host["A"], host["B"], s)
+    dx_ref, dA_ref, dB_ref = O.lora_linear_grads(host["x"], host["w0"], host["b"], host["A"], host["B"], s, host["dy"])
+    errs = {"y": rel_err(y, y_ref), "T": rel_err(T, host["x"] @ host["A"].t()),
+            "dT": rel_err(dT, host["dy"] @ host["B"]), "dx": rel_err(dx, dx_ref)}
+    if s != 0.0:
+        errs["dA"] = rel_err(dA, dA_ref)
+        errs["dB"] = rel_err(dB, dB_ref)
+    else:
+        assert dA.abs().max() == 0 and dB.abs().max() == 0
+    bad = {k: v for k, v in errs.items() if not v < tol}
+    assert not bad, f"{tag}: rel-err over tolerance {tol}: {bad} (all: {errs})"
+
+
+# (M, K, N, r, bias, scale): ragged M, N not a multiple of the tile, K not a multiple of 64
+SHAPES = [
+    (256, 64, 64, 4, False, 1.0),
+    (128, 128, 160, 4, True, 0.7),
+    (300, 320, 320, 4, True, 1.0),
+    (77 * 2, 768, 320, 1, False, 1.0),
+    (1000, 320, 2560, 16, True, 0.5),
+    (130, 72, 40, 4, False, 0.0),
+    (513, 200, 328, 8, True, 1.3),
+    (4096, 640, 640, 4, False, 1.0),
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_simt_fp32_matches_oracle(shape):
+    M, K, N, r, bias, s = shape
+    host, dev = make_case(M, K, N, r, bias, torch.float32, seed=M + K)
+    check_against_oracle(host, run_cabi(dev, M, K, N, r, s, torch.float32, nat.IMPL_SIMT), s, 1e-5, "simt/f32")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", SHAPES)
+def test_tcgen05_matches_oracle(shape, dtype):
+    M, K, N, r, bias, s = shape
+    host, dev = make_case(M, K, N, r, bias, dtype, seed=M + N)
+    check_against_oracle(host, run_cabi(dev, M, K, N, r, s, dtype, nat.IMPL_TC), s, 2e-2, f"tc/{dtype}")
+
+
+@pytest.mark.parametrize("shape", SHAPES[:4])
+def test_simt_bf16_matches_oracle(shape):
+    M, K, N, r, bias, s = shape
+    host, dev = make_case(M, K, N, r, bias, torch.bfloat16, seed=M)
+    check_against_oracle(host, run_cabi(dev, M, K, N, r, s, torch.bfloat16, nat.IMPL_SIMT), s, 2e-2, "simt/bf16")
+
+
+def test_tc_tighter_than_tolerance_and_fp32_masters():
+    """fp32 accumulation end to end: the fused kernel should sit well inside the 2e-2 bar, and
+    reads fp32 LoRA masters directly (autocast layout)."""
+    M, K, N, r = 2048, 1280, 1280, 4
+    host, dev = make_case(M, K, N, r, True, torch.bfloat16, seed=11, ab_dtype=torch.float32)
+    y, T, dx, dT, dA, dB = run_cabi(dev, M, K, N, r, 1.0, torch.bfloat16, nat.IMPL_TC)
+    y_ref = O.lora_linear_forward(host["x"], host["w0"], host["b"], host["A"], host["B"], 1.0)
+    assert rel_err(y, y_ref) < 4e-3
+
+
+def test_golden_reference_vectors_fp32():
+    """The reference's own outputs (tests/golden/linear_cases) through the autograd op."""
+    blob, _ = load_golden("linear_cases.safetensors")
+    for i, (lead, K, N, r, bias, s) in enumerate(LINEAR_CASES):
+        g = lambda k: blob.get(f"c{i}.{k}")
+        m = L.LoraInjectedLinear(K, N, bias, r).to(DEV)
+        with torch.no_grad():
+            m.linear.weight.copy_(g("w0"))
+            if bias:
+                m.linear.bias.copy_(g("b"))
+            m.lora_down.weight.copy_(g("A"))
+            m.lora_up.weight.copy_(g("B"))
+        m.linear.requires_grad_(False)
+        m.scale = s
+        x = g("x").to(DEV).requires_grad_(True)
+        y = m(x)
+        y.backward(g("dy").to(DEV))
+        assert y.shape == g("y").shape
+        assert rel_err(y, g("y")) < 1e-5 and rel_err(x.grad, g("dx")) < 1e-5
+        if s != 0.0:
+            assert rel_err(m.lora_down.weight.grad, g("dA")) < 1e-5
+            assert rel_err(m.lora_up.weight.grad, g("dB")) < 1e-5
+
+
+def test_module_modes_noncontiguous_nograd_autocast_deterministic():
+    torch.manual_seed(3)
+    m = L.LoraInjectedLinear(320, 640, bias=True, r=4).to(DEV)
+    m.linear.requires_grad_(False)
+    with torch.no_grad():
+        m.lora_up.weight.normal_(0, 0.02)
+    ref = O.OracleLoraLinear(320, 640, True, 4)
+    ref.load_state_dict({k: v.cpu() for k, v in m.state_dict().items()})
+    xb = torch.randn(4, 320, 50, device=DEV).transpose(1, 2)       # non-contiguous [4,50,320]
+    assert not xb.is_contiguous()
+    with torch.no_grad():
+        y = m(xb)
+    assert rel_err(y, ref(xb.cpu())) < 1e-5
+    # autocast with fp32 masters (the reference's real mixed-precision mode)
+    x = torch.randn(3, 77, 320, device=DEV, requires_grad=True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y = m(x)
+    assert y.dtype == torch.bfloat16
+    y.float().square().mean().backward()
+    xr = x.detach().cpu().requires_grad_(True)
+    yr = ref(xr)
+    yr.square().mean().backward()
+    assert rel_err(y, yr) < 2e-2 and rel_err(x.grad, xr.grad) < 2e-2
+    assert m.lora_up.weight.grad.dtype == torch.float32
+    assert rel_err(m.lora_up.weight.grad, ref.lora_up.weight.grad) < 2e-2
+    assert rel_err(m.lora_down.weight.grad, ref.lora_down.weight.grad) < 2e-2
+    # tune scale at run time, deterministic reductions are bit-reproducible
+    L.tune_lora_scale(m, 0.25)
+    outs = []
+    for _ in range(2):
+        m.zero_grad()
+        x2 = torch.randn(2, 300, 320, device=DEV, generator=torch.Generator(DEV).manual_seed(5))
+        ops.lora_linear(x2, m.linear.weight, m.linear.bias, m.lora_down.weight, m.lora_up.weight, m.scale,
+                        deterministic=True).sum().backward()
+        outs.append((m.lora_down.weight.grad.clone(), m.lora_up.weight.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+def test_full_size_properties_bf16():
+    """BASELINE full-size shape (32768 x 320 -> 320): size-independent properties instead of a CPU
+    oracle run — linearity in scale and agreement of the two kernel families."""
+    M, K, N, r = 32768, 320, 320, 4
+    _, dev = make_case(M, K, N, r, True, torch.bfloat16, seed=1)
+    y_tc, T_tc, dx_tc, *_ = run_cabi(dev, M, K, N, r, 1.0, torch.bfloat16, nat.IMPL_TC)
+    y_si, T_si, dx_si, *_ = run_cabi(dev, M, K, N, r, 1.0, torch.bfloat16, nat.IMPL_SIMT)
+    assert rel_err(y_tc, y_si.float()) < 1e-2 and rel_err(dx_tc, dx_si.float()) < 1e-2
+    y0, *_ = run_cabi(dev, M, K, N, r, 0.0, torch.bfloat16, nat.IMPL_TC)
+    y2, *_ = run_cabi(dev, M, K, N, r, 2.0, torch.bfloat16, nat.IMPL_TC)
+    lhs = (y2.float() - y0.float())
+    rhs = 2.0 * (y_tc.float() - y0.float())
+    assert rel_err(lhs, rhs) < 5e-2      # branch is ~1e-2 of the output; bf16 rounding of y dominates

@@ -1,0 +1,116 @@
+"""Whole-model parity (BASELINE config 1) and the utility kernels on the GPU."""
+import json
+
+import pytest
+import torch
+
+import diffusion_finetuning_b200 as L
+from conftest import load_golden, rel_err
+from diffusion_finetuning_b200 import ops
+from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
+from oracle import lora_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_config1_tiny_unet_matches_reference_vectors():
+    """inject_trainable_lora r=4 into the tiny UNet, 32x32 latents, batch 2: our CUDA path against
+    what the reference produced on the CPU (tests/golden/tiny_unet_step)."""
+    blob, meta = load_golden("tiny_unet_step.safetensors")
+    torch.manual_seed(0)
+    unet = UNet2DConditionModel.tiny()
+    unet.requires_grad_(False)
+    torch.manual_seed(1)
+    _, names = L.inject_trainable_lora(unet, r=4)
+    assert names == json.loads(meta["names"])
+    layers = [m for m in unet.modules() if isinstance(m, L.LoraInjectedLinear)]
+    with torch.no_grad():
+        for i, m in enumerate(layers):
+            m.lora_up.weight.copy_(blob[f"up{i}"])
+    unet.to(DEV)
+    prev = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False     # keep the stock convs in true fp32 for the comparison
+    try:
+        pred = unet(blob["latents"].to(DEV), blob["timesteps"].to(DEV), blob["context"].to(DEV))
+        loss = torch.nn.functional.mse_loss(pred, blob["target"].to(DEV))
+        loss.backward()
+    finally:
+        torch.backends.cudnn.allow_tf32 = prev
+    assert rel_err(pred, blob["pred"]) < 1e-4
+    assert abs(loss.item() - blob["loss"].item()) < 1e-4
+    worst = 0.0
+    for i, m in enumerate(layers):
+        worst = max(worst, rel_err(m.lora_up.weight.grad, blob[f"gup{i}"]),
+                    rel_err(m.lora_down.weight.grad, blob[f"gdown{i}"]))
+    assert worst < 1e-3, worst     # stock conv/attention kernels in between add their own rounding
+
+
+def test_merge_kernel_matches_reference_vectors():
+    blob, meta = load_golden("merge_cases.safetensors")
+    alpha = float(meta["alpha"])
+    for tag in ("f32", "f16"):
+        for w, u, d, want in ((f"{tag}.w_q", f"{tag}.lora0", f"{tag}.lora1", f"{tag}.merged_q"),
+                              (f"{tag}.w_o", f"{tag}.lora2", f"{tag}.lora3", f"{tag}.merged_o")):
+            got = ops.merge_lora_weight(blob[w].to(DEV), blob[u].to(DEV), blob[d].to(DEV), alpha)
+            # within fp32 rounding of the reference's result (summation order of the rank-4 product)
+            assert torch.allclose(got.cpu(), blob[want], rtol=0, atol=2e-7 if tag == "f32" else 1e-4), tag
+            host = ops.merge_lora_weight(blob[w], blob[u], blob[d], alpha)      # host buffers staged through the GPU
+            assert host.device.type == "cpu" and torch.equal(host, got.cpu())
+
+
+@pytest.mark.parametrize("wdt", [torch.float32, torch.float16, torch.bfloat16])
+def test_merge_kernel_shapes_and_dtypes(wdt):
+    g = torch.Generator().manual_seed(0)
+    for (N, K, r) in ((1280, 1280, 4), (10240, 1280, 16), (320, 768, 1)):
+        W = (torch.randn(N, K, generator=g) * 0.03).to(wdt)
+        up = torch.randn(N, r, generator=g) * 0.05
+        down = torch.randn(r, K, generator=g) * 0.3
+        got = ops.merge_lora_weight(W.to(DEV), up.to(DEV), down.to(DEV), 0.6)
+        want = O.merge_weight(W, up, down, 0.6)
+        assert got.dtype == wdt
+        assert rel_err(got, want.float()) < (1e-6 if wdt == torch.float32 else 3e-3)
+
+
+def test_weight_apply_lora_and_inspect_and_collapse():
+    class CrossAttention(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.to_q = torch.nn.Linear(64, 96, bias=False)
+            self.to_k = torch.nn.Linear(64, 96, bias=False)
+
+    torch.manual_seed(0)
+    a = torch.nn.Sequential(CrossAttention()).to(DEV)
+    b = torch.nn.Sequential(CrossAttention())
+    b.load_state_dict({k: v.cpu() for k, v in a.state_dict().items()})
+    loras = [torch.randn(96, 4) * 0.1, torch.randn(4, 64), torch.randn(96, 4) * 0.1, torch.randn(4, 64)]
+    L.weight_apply_lora(a, [t.clone() for t in loras], {"CrossAttention"}, alpha=0.5)
+    for lin, (u, d) in zip((b[0].to_q, b[0].to_k), ((loras[0], loras[1]), (loras[2], loras[3]))):
+        lin.weight = torch.nn.Parameter(O.merge_weight(lin.weight, u, d, 0.5))
+    assert torch.allclose(a[0].to_q.weight.cpu(), b[0].to_q.weight, atol=1e-6)
+    assert torch.allclose(a[0].to_k.weight.cpu(), b[0].to_k.weight, atol=1e-6)
+    assert isinstance(a[0].to_q.weight, torch.nn.Parameter) and a[0].to_q.weight.requires_grad
+    L.monkeypatch_lora(a, [t.clone() for t in loras], {"CrossAttention"}, r=4)
+    moved = L.inspect_lora(a)
+    assert abs(moved["0.to_q"][0] - O.lora_abs_mean(loras[0], loras[1])) < 1e-5
+    x = torch.randn(5, 64, device=DEV)
+    with torch.no_grad():
+        y_lora = a[0].to_q(x)
+        L.collapse_lora(a)
+        L.tune_lora_scale(a, 0.0)
+        y_merged = a[0].to_q(x)
+    assert rel_err(y_merged, y_lora) < 1e-5
+
+
+def test_svd_distill_matches_oracle():
+    g = torch.Generator().manual_seed(3)
+    up = torch.randn(320, 4, generator=g) * 0.05
+    down = torch.randn(4, 768, generator=g) * 0.5
+    delta = (up @ down + 1e-4 * torch.randn(320, 768, generator=g)).half()
+    U, Vh = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=0.99)
+    Uo, Vo = O.svd_distill_matrix(delta, rank=4, clamp_quantile=0.99)
+    assert U.dtype == torch.float32 and tuple(U.shape) == (320, 4) and tuple(Vh.shape) == (4, 768)
+    # factors are defined up to sign / rotation inside equal singular values: compare products
+    assert rel_err(U @ Vh, Uo @ Vo) < 1e-3
+    assert abs(max(U.abs().max().item(), Vh.abs().max().item())
+               - max(Uo.abs().max().item(), Vo.abs().max().item())) < 1e-4
