@@ -26,8 +26,9 @@ int tc_pick_bn(int Nout);
 int tc_smem_bytes(int BN, int* stages_out);
 unsigned int tc_read_watchdog();
 template <typename TIO>
-cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const TcParams&,
-                      int, int, cudaStream_t);
+cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                      const TcParams&, int, int, cudaStream_t);
+cudaError_t launch_pack(const void*, const void*, int, void*, void*, int, int, int, int, cudaStream_t);
 template <typename TIO>
 cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
                         const void*, long long, long long, const void*, long long, long long, int,
@@ -148,7 +149,7 @@ static bool tc_applicable(const void* X, long long ldx, const void* W, long long
 }
 
 static int run_tc(const void* X, long long ldx, const void* W, long long ldw, const void* bias,
-                  int bias_dtype, const void* S1, long long s1_rs, long long s1_cs, const void* S2,
+                  int bias_dtype, const void* S1_pack, const void* S2,
                   long long s2_rs, long long s2_cs, int ab_dtype, float scale, void* Y,
                   long long ldy, void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
                   cudaStream_t stream) {
@@ -162,7 +163,7 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, co
   const int smem = tc_smem_bytes(p.BN, &p.stages);
   if (p.stages < 2) { set_error("tc: not enough shared memory for BN=%d", p.BN); return B200LORA_E_SHAPE; }
   p.scale = scale;
-  p.S1 = S1; p.s1_rs = s1_rs; p.s1_cs = s1_cs;
+  p.S1 = S1_pack; p.s1_rs = Kc; p.s1_cs = 1;
   p.S2 = S2; p.s2_rs = s2_rs; p.s2_cs = s2_cs;
   p.ab_dtype = ab_dtype; p.bias = bias; p.bias_dtype = bias_dtype; p.T_out = T_out;
   const unsigned fmt = io_dtype == B200LORA_BF16 ? 1u : 0u;
@@ -170,18 +171,20 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, co
   p.idesc_main = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)(p.BN + 16) >> 3) << 17) | ((128u >> 4) << 24);
   p.idesc_tail = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)p.BN >> 3) << 17) | ((128u >> 4) << 24);
 
-  CUtensorMap tmX, tmW, tmY;
+  CUtensorMap tmX, tmW, tmS, tmY;
   int rc;
   if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmW, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)p.BN, 64,
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmS, S1_pack, 16, (uint64_t)Kc, (uint64_t)Kc, 16, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   DevInfo di = dev_info();
   cudaError_t e = io_dtype == B200LORA_BF16
-                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmY, p, smem, di.sms, stream)
-                      : launch_tc<__half>(tmX, tmW, tmY, p, smem, di.sms, stream);
+                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmS, tmY, p, smem, di.sms, stream)
+                      : launch_tc<__half>(tmX, tmW, tmS, tmY, p, smem, di.sms, stream);
   if (e != cudaSuccess) {
     set_error("tc launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
@@ -225,15 +228,30 @@ extern "C" int b200lora_tc_supported(void) {
 // diagnostic: non-zero if the tensor-core kernel's watchdog fired (site<<16 | block)
 extern "C" unsigned int b200lora_watchdog_code(void) { return tc_read_watchdog(); }
 
-extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int64_t ldw,
-                                  int w_layout, const void* bias, int bias_dtype, const void* S1,
-                                  int64_t s1_rs, int64_t s1_cs, const void* S2, int64_t s2_rs,
-                                  int64_t s2_cs, int ab_dtype, float scale, void* Y, int64_t ldy,
-                                  void* T_out, int64_t M, int Kc, int Nout, int r, int io_dtype,
-                                  int impl, b200lora_stream_t stream_) {
+extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, void* A_pack,
+                                  void* Bt_pack, int K, int N, int r, int io_dtype,
+                                  b200lora_stream_t stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   g_err[0] = 0;
-  if (!X || !W || !S1 || !S2 || !Y) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!A || !B || !A_pack || !Bt_pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(ab_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
+    set_error("pack_lora: io dtype must be bf16/fp16"); return B200LORA_E_DTYPE;
+  }
+  if (K < 1 || N < 1 || r < 1 || r > 16) { set_error("pack_lora: needs 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  cudaError_t e = launch_pack(A, B, ab_dtype, A_pack, Bt_pack, K, N, r, io_dtype, stream);
+  if (e != cudaSuccess) { set_error("pack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int64_t ldw,
+                                  int w_layout, const void* bias, int bias_dtype, const void* S1,
+                                  int64_t s1_rs, int64_t s1_cs, const void* S1_pack, const void* S2,
+                                  int64_t s2_rs, int64_t s2_cs, int ab_dtype, float scale, void* Y,
+                                  int64_t ldy, void* T_out, int64_t M, int Kc, int Nout, int r,
+                                  int io_dtype, int impl, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!X || !W || !S2 || !Y || (!S1 && !S1_pack)) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (!valid_dtype(io_dtype) || !valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype))) {
     set_error("bad dtype enum"); return B200LORA_E_DTYPE;
   }
@@ -244,10 +262,15 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
     set_error("leading dimension smaller than the row length"); return B200LORA_E_SHAPE;
   }
   if (impl == B200LORA_IMPL_TC || impl == B200LORA_IMPL_AUTO) {
-    const bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype);
+    bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype);
+    if (ok && (!S1_pack || !aligned16(S1_pack) || (Kc % 8))) {
+      set_error("tc path needs the packed rank rows (b200lora_pack_lora) 16-byte aligned");
+      ok = false;
+      if (impl == B200LORA_IMPL_TC) return B200LORA_E_ARG;
+    }
     if (ok)
-      return run_tc(X, ldx, W, ldw, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs, ab_dtype,
-                    scale, Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
+      return run_tc(X, ldx, W, ldw, bias, bias_dtype, S1_pack, S2, s2_rs, s2_cs, ab_dtype, scale, Y,
+                    ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
     if (impl == B200LORA_IMPL_TC) {
       if (io_dtype == B200LORA_F32) return B200LORA_E_DTYPE;
       DevInfo di = dev_info();
@@ -256,29 +279,30 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
     }
     g_err[0] = 0;
   }
+  if (!S1) { set_error("simt path needs the unpacked rank rows S1"); return B200LORA_E_ARG; }
   return run_simt(X, ldx, W, ldw, w_layout, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs,
                   ab_dtype, scale, Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
 }
 
 extern "C" int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
-                                   const void* A, const void* B, int ab_dtype, float scale, void* Y,
-                                   void* T_out, int64_t M, int K, int N, int r, int io_dtype,
-                                   int impl, b200lora_stream_t stream) {
+                                   const void* A, const void* B, int ab_dtype, const void* A_pack,
+                                   float scale, void* Y, void* T_out, int64_t M, int K, int N,
+                                   int r, int io_dtype, int impl, b200lora_stream_t stream) {
   // S1 = A [r,K] (row stride K), S2 = B [N,r] (row stride r)
-  return b200lora_lora_gemm(X, K, W0, K, B200LORA_W_NK, bias, bias_dtype, A, K, 1, B, r, 1,
+  return b200lora_lora_gemm(X, K, W0, K, B200LORA_W_NK, bias, bias_dtype, A, K, 1, A_pack, B, r, 1,
                             ab_dtype, scale, Y, N, T_out, M, K, N, r, io_dtype, impl, stream);
 }
 
 extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout, const void* A,
-                                      const void* B, int ab_dtype, float scale, void* dX,
-                                      void* dT_out, int64_t M, int K, int N, int r, int io_dtype,
-                                      int impl, b200lora_stream_t stream) {
+                                      const void* B, int ab_dtype, const void* Bt_pack, float scale,
+                                      void* dX, void* dT_out, int64_t M, int K, int N, int r,
+                                      int io_dtype, int impl, b200lora_stream_t stream) {
   // dX = dY·W0 + (s·dY·B)·A : contraction over N.  S1 = Bᵀ (logical [r,N]: (j,n) -> B[n*r+j]),
   // S2 = Aᵀ (logical [K,r]: (k,j) -> A[j*K+k]).  W as [K,N] (NK layout of the transposed
   // problem) or W0 itself [N,K] (KN layout).
   const int64_t ldw = (w_layout == B200LORA_W_NK) ? N : K;
-  return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, A, 1, K, ab_dtype, scale,
-                            dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+  return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, Bt_pack, A, 1, K,
+                            ab_dtype, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
 }
 
 extern "C" int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r) {

@@ -31,6 +31,7 @@ constexpr int UK = 16;           // UMMA K for 16-bit inputs
 constexpr int ACC_STRIDE = 256;  // TMEM columns per accumulator stage
 constexpr int EPI_COLS = 32;     // columns per epilogue staging unit / TMA store box
 constexpr int MAX_STAGES = 8;
+constexpr int MAX_CHUNKS = 7;     // BN <= 224
 constexpr int NUM_THREADS = 256;
 
 constexpr int A_TILE_BYTES = BM * 128;                 // 16 KB
@@ -68,7 +69,8 @@ enum : uint32_t {
 template <typename TIO>
 __global__ void __launch_bounds__(tc::NUM_THREADS, 1)
 lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
-                    const __grid_constant__ CUtensorMap tmY, const TcParams p) {
+                    const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmY,
+                    const TcParams p) {
   using namespace tc;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve (dynamic smem base is only guaranteed 16B aligned by the ABI -> align by hand)
@@ -99,11 +101,12 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX);
     tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmS);
     tma_prefetch_desc(&tmY);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full_bar[s], 2);   // TMA thread (arrive.expect_tx) + loader warp
+      mbar_init(&full_bar[s], 1);   // TMA thread (arrive.expect_tx)
       mbar_init(&empty_bar[s], 1);  // tcgen05.commit
     }
     for (int a = 0; a < 2; ++a) {
@@ -131,7 +134,7 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       const uint64_t pol_w = policy_evict_last();
       int s = 0;
       uint32_t ph = 0;
-      const uint32_t tx_bytes = A_TILE_BYTES + BN * 128;
+      const uint32_t tx_bytes = A_TILE_BYTES + (BN + RP) * 128;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int n_blk = tile % p.num_n_blk;
         const int m_blk = tile / p.num_n_blk;
@@ -142,6 +145,8 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
           tma_load_2d(a_dst, &tmX, &full_bar[s], kb * BK, m_blk * BM, pol_x);
           tma_load_2d(b_dst, &tmW, &full_bar[s], kb * BK, n_blk * BN, pol_w);
+          // the 16 rank rows (packed [16,Kc], zero padded) land right behind the W rows
+          tma_load_2d(b_dst + (size_t)BN * 128, &tmS, &full_bar[s], kb * BK, 0, pol_w);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
@@ -186,44 +191,9 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     }
   } else if (warp == 2) {
     // =============================== small-operand loader =============================
-    // zero the padding rows r..15 of the S1 block of every stage once
-    for (int s = 0; s < stages; ++s) {
-      uint8_t* rows = stage_base + (size_t)s * stg_bytes + A_TILE_BYTES + (size_t)BN * 128;
-      for (int slot = lane; slot < RP * 8; slot += 32) {
-        const int j = slot >> 3;
-        if (j >= p.r) *reinterpret_cast<uint4*>(rows + slot * 16) = make_uint4(0, 0, 0, 0);
-      }
-    }
-    int s = 0;
-    uint32_t ph = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int n_blk = tile % p.num_n_blk;
-      for (int kb = 0; kb < p.num_k_blk; ++kb) {
-        mbar_wait(&empty_bar[s], ph ^ 1, SITE_LD_EMPTY);
-        uint8_t* rows = stage_base + (size_t)s * stg_bytes + A_TILE_BYTES + (size_t)BN * 128;
-        // r rows x 8 chunks of 8 elements; chunk c of row j lands at j*128 + ((c ^ (j&7))<<4)
-        for (int slot = lane; slot < p.r * 8; slot += 32) {
-          const int j = slot >> 3, c = slot & 7;
-          const int k0 = kb * BK + c * 8;
-          float v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int k = k0 + e;
-            v[e] = (k < p.Kc) ? load_as_float(p.S1, p.ab_dtype, j * p.s1_rs + k * p.s1_cs) : 0.f;
-          }
-          uint4 q;
-          q.x = pack2<TIO>(v[0], v[1]);
-          q.y = pack2<TIO>(v[2], v[3]);
-          q.z = pack2<TIO>(v[4], v[5]);
-          q.w = pack2<TIO>(v[6], v[7]);
-          *reinterpret_cast<uint4*>(rows + j * 128 + ((c ^ (j & 7)) << 4)) = q;
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&full_bar[s]);
-        if (++s == stages) { s = 0; ph ^= 1; }
-      }
       // S2 tile for this output tile: BN rows x 16 k (k >= r zero), rows >= Nout zero
       mbar_wait(bs_empty_bar, (it & 1) ^ 1, SITE_LD_BS_EMPTY);
       for (int n = lane; n < BN; n += 32) {
@@ -272,7 +242,10 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         tmem_ld_x16(acc_addr + BN, tv);
         tmem_ld_wait();
         if (t_out != nullptr && n_blk == 0 && gm < p.M) {
-          for (int j = 0; j < p.r; ++j) t_out[gm * p.r + j] = TIO(__uint_as_float(tv[j]));
+          TIO* trow_out = t_out + gm * p.r;
+#pragma unroll
+          for (int j = 0; j < 16; ++j)   // static register indexing; r is warp-uniform
+            if (j < p.r) trow_out[j] = TIO(__uint_as_float(tv[j]));
         }
         float tf[16];
 #pragma unroll
@@ -291,44 +264,53 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       }
 
       // ---- accumulator: TMEM -> regs -> (+bias, round) -> swizzled staging -> TMA store ----
+      // bias for this tile: lane e of chunk c holds bias[n0 + 32c + e]; fetched before the
+      // accumulator wait so the latency hides behind the tail MMA, broadcast by shuffle later
+      const int n_chunks = BN / EPI_COLS;
+      float bias_reg[MAX_CHUNKS];
+#pragma unroll
+      for (int c = 0; c < MAX_CHUNKS; ++c) {
+        const int gn = n_blk * BN + c * EPI_COLS + lane;
+        bias_reg[c] = (p.bias != nullptr && c < n_chunks && gn < p.Nout)
+                          ? load_as_float(p.bias, p.bias_dtype, gn) : 0.f;
+      }
       mbar_wait(&accfull_bar[a], aph, SITE_EPI_ACC);
       tc_fence_after_sync();
-      const int n_chunks = BN / EPI_COLS;
-      for (int c = 0; c < n_chunks; ++c) {
+#pragma unroll
+      for (int c = 0; c < MAX_CHUNKS; ++c) {
         const int gn0 = n_blk * BN + c * EPI_COLS;
-        if (gn0 >= p.Nout) break;  // fully out-of-range chunk (ragged N)
-        uint32_t v[32];
-        tmem_ld_x32(acc_addr + c * EPI_COLS, v);
-        // staging buffer `buf` may still be read by the TMA store issued two chunks ago
-        if (lane == 0) tma_store_wait_read<1>();
-        __syncwarp();
-        tmem_ld_wait();
-        if (p.bias != nullptr) {
+        if (c < n_chunks && gn0 < p.Nout) {   // warp-uniform
+          uint32_t v[32];
+          tmem_ld_x32(acc_addr + c * EPI_COLS, v);
+          // staging buffer `buf` may still be read by the TMA store issued two chunks ago
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          tmem_ld_wait();
+          if (p.bias != nullptr) {
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int gn = gn0 + e;
-            const float b = (gn < p.Nout) ? load_as_float(p.bias, p.bias_dtype, gn) : 0.f;
-            v[e] = __float_as_uint(__uint_as_float(v[e]) + b);
+            for (int e = 0; e < 32; ++e)
+              v[e] = __float_as_uint(__uint_as_float(v[e]) +
+                                     __shfl_sync(0xffffffffu, bias_reg[c], e));
           }
-        }
-        uint8_t* srow = my_staging + buf * (32 * EPI_COLS * 2) + lane * 64;
-        const int sw = (lane >> 1) & 3;  // 64B swizzle: 16B-chunk index ^= address bits [7,9)
+          uint8_t* srow = my_staging + buf * (32 * EPI_COLS * 2) + lane * 64;
+          const int sw = (lane >> 1) & 3;  // 64B swizzle: 16B-chunk index ^= address bits [7,9)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 o;
-          o.x = pack2<TIO>(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]));
-          o.y = pack2<TIO>(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]));
-          o.z = pack2<TIO>(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]));
-          o.w = pack2<TIO>(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]));
-          *reinterpret_cast<uint4*>(srow + ((q ^ sw) << 4)) = o;
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            o.x = pack2<TIO>(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]));
+            o.y = pack2<TIO>(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]));
+            o.z = pack2<TIO>(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]));
+            o.w = pack2<TIO>(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]));
+            *reinterpret_cast<uint4*>(srow + ((q ^ sw) << 4)) = o;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmY, my_staging + buf * (32 * EPI_COLS * 2), gn0, m_blk * BM + ew * 32);
+            tma_store_commit();
+          }
+          buf ^= 1;
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_2d(&tmY, my_staging + buf * (32 * EPI_COLS * 2), gn0, m_blk * BM + ew * 32);
-          tma_store_commit();
-        }
-        buf ^= 1;
       }
       // all TMEM reads of this accumulator stage are complete (tmem_ld_wait above)
       tc_fence_before_sync();
@@ -374,8 +356,9 @@ int tc_smem_bytes(int BN, int* stages_out) {
 }
 
 template <typename TIO>
-cudaError_t launch_tc(const CUtensorMap& tmX, const CUtensorMap& tmW, const CUtensorMap& tmY,
-                      const TcParams& p, int smem_bytes, int num_sms, cudaStream_t stream) {
+cudaError_t launch_tc(const CUtensorMap& tmX, const CUtensorMap& tmW, const CUtensorMap& tmS,
+                      const CUtensorMap& tmY, const TcParams& p, int smem_bytes, int num_sms,
+                      cudaStream_t stream) {
   auto kern = lora_gemm_tc_kernel<TIO>;
   static thread_local int configured_smem = 0;
   if (configured_smem < smem_bytes) {
@@ -386,15 +369,16 @@ cudaError_t launch_tc(const CUtensorMap& tmX, const CUtensorMap& tmW, const CUte
   }
   const int num_tiles = p.num_m_blk * p.num_n_blk;
   const int grid = num_tiles < num_sms ? num_tiles : num_sms;
-  kern<<<grid, tc::NUM_THREADS, smem_bytes, stream>>>(tmX, tmW, tmY, p);
+  kern<<<grid, tc::NUM_THREADS, smem_bytes, stream>>>(tmX, tmW, tmS, tmY, p);
   return cudaGetLastError();
 }
 
 template cudaError_t launch_tc<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&,
-                                              const CUtensorMap&, const TcParams&, int, int,
-                                              cudaStream_t);
+                                              const CUtensorMap&, const CUtensorMap&,
+                                              const TcParams&, int, int, cudaStream_t);
 template cudaError_t launch_tc<__half>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                                       const TcParams&, int, int, cudaStream_t);
+                                       const CUtensorMap&, const TcParams&, int, int,
+                                       cudaStream_t);
 
 unsigned int tc_read_watchdog() {
   unsigned int v = 0;

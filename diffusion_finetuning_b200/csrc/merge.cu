@@ -155,4 +155,38 @@ cudaError_t launch_svd_epilogue(float* U, const float* S, float* Vh, float hi, i
   return cudaGetLastError();
 }
 
+// ---- LoRA pack: A -> A_pack [16,K], B -> Bt_pack [16,N] (= Bᵀ), both in the io dtype with rows
+// r..15 zero.  These are the TMA-loadable "rank rows" of the fused GEMM (forward uses A_pack,
+// backward-dX uses Bt_pack).  One launch per (A,B) version; O(16·(K+N)) elements.
+template <typename TIO>
+__global__ void lora_pack_kernel(const void* __restrict__ A, const void* __restrict__ B, int ab_dtype,
+                                 TIO* __restrict__ A_pack, TIO* __restrict__ Bt_pack, int K, int N,
+                                 int r) {
+  const int total = 16 * (K + N);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    if (i < 16 * K) {
+      const int j = i / K, k = i - j * K;
+      A_pack[i] = from_f32<TIO>(j < r ? load_as_float(A, ab_dtype, (long long)j * K + k) : 0.f);
+    } else {
+      const int t = i - 16 * K;
+      const int j = t / N, n = t - j * N;
+      Bt_pack[t] = from_f32<TIO>(j < r ? load_as_float(B, ab_dtype, (long long)n * r + j) : 0.f);
+    }
+  }
+}
+
+cudaError_t launch_pack(const void* A, const void* B, int ab_dtype, void* A_pack, void* Bt_pack,
+                        int K, int N, int r, int io_dtype, cudaStream_t stream) {
+  const int total = 16 * (K + N);
+  int blocks = (total + 255) / 256;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (io_dtype == B200LORA_BF16)
+    lora_pack_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
+        A, B, ab_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack, K, N, r);
+  else
+    lora_pack_kernel<__half><<<blocks, 256, 0, stream>>>(A, B, ab_dtype, (__half*)A_pack,
+                                                         (__half*)Bt_pack, K, N, r);
+  return cudaGetLastError();
+}
+
 }  // namespace b200

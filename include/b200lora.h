@@ -72,6 +72,9 @@ int b200lora_tc_supported(void);
  * S1[j*s1_rs + k*s1_cs], S2 logical [Nout,r] with element (n,j) at S2[n*s2_rs + j*s2_cs].
  * io_dtype is the type of X, W, Y and T_out; ab_dtype the type of S1/S2 (fp32 masters
  * under autocast are read directly); bias may be NULL.
+ * The tcgen05 path fetches the rank rows by TMA from S1_pack (see b200lora_pack_lora) and
+ * ignores S1; the SIMT path reads S1 with its strides and ignores S1_pack.  Either may be NULL
+ * if the selected path does not need it.
  * On the tcgen05 path this is ONE kernel: the rank-r rows ride along as 16 extra
  * accumulator columns of the same MMA and the up-projection is one more K=16 MMA step
  * ([X | sT]·[Wᵀ ; S2ᵀ]), so no separate low-rank GEMM or elementwise add runs.
@@ -80,6 +83,7 @@ int b200lora_lora_gemm(const void* X, int64_t ldx,
                        const void* W, int64_t ldw, int w_layout,
                        const void* bias, int bias_dtype,
                        const void* S1, int64_t s1_rs, int64_t s1_cs,
+                       const void* S1_pack /* [16,Kc] io dtype, rows >= r zero; tcgen05 path */,
                        const void* S2, int64_t s2_rs, int64_t s2_cs, int ab_dtype,
                        float scale,
                        void* Y, int64_t ldy,
@@ -88,13 +92,25 @@ int b200lora_lora_gemm(const void* X, int64_t ldx,
                        int io_dtype, int impl, b200lora_stream_t stream);
 
 /*
+ * Pack the LoRA factors for the tcgen05 path (one tiny launch per weight version):
+ *   A_pack  [16,K] = A  (lora_down.weight [r,K]) zero-padded to 16 rows, in io_dtype
+ *   Bt_pack [16,N] = Bᵀ (lora_up.weight   [N,r]) zero-padded to 16 rows, in io_dtype
+ * These are the TMA-loadable rank rows that ride along as 16 extra MMA columns; fp32 masters
+ * (autocast) are rounded to io_dtype here, as autocast would round them.
+ */
+int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, void* A_pack, void* Bt_pack,
+                       int K, int N, int r, int io_dtype, b200lora_stream_t stream);
+
+/*
  * Forward of LoraInjectedLinear — replaces lora.py:49-50
  *   `self.linear(input) + self.lora_up(self.lora_down(input)) * self.scale`
  * (3 F.linear + mul + add in the reference; one kernel here).
  * T_out (nullable) receives T = X·Aᵀ for the backward; pass NULL under no_grad.
  */
 int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
-                        const void* A, const void* B, int ab_dtype, float scale,
+                        const void* A, const void* B, int ab_dtype,
+                        const void* A_pack /* from b200lora_pack_lora; NULL on the SIMT path */,
+                        float scale,
                         void* Y, void* T_out,
                         int64_t M, int K, int N, int r,
                         int io_dtype, int impl, b200lora_stream_t stream);
@@ -107,7 +123,9 @@ int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bia
  *   B200LORA_W_KN: W is W0 itself [N,K] (accepted by the SIMT path only)
  */
 int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout,
-                           const void* A, const void* B, int ab_dtype, float scale,
+                           const void* A, const void* B, int ab_dtype,
+                           const void* Bt_pack /* from b200lora_pack_lora; NULL on the SIMT path */,
+                           float scale,
                            void* dX, void* dT_out,
                            int64_t M, int K, int N, int r,
                            int io_dtype, int impl, b200lora_stream_t stream);

@@ -107,10 +107,22 @@ def test_svd_distill_matches_oracle():
     up = torch.randn(320, 4, generator=g) * 0.05
     down = torch.randn(4, 768, generator=g) * 0.5
     delta = (up @ down + 1e-4 * torch.randn(320, 768, generator=g)).half()
-    U, Vh = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=0.99)
-    Uo, Vo = O.svd_distill_matrix(delta, rank=4, clamp_quantile=0.99)
+    # without the clamp the factorisation is unique up to the sign of each singular pair:
+    # compare the products (cli_svd.py:69-77)
+    U, Vh = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=1.0)
+    Uo, Vo = O.svd_distill_matrix(delta, rank=4, clamp_quantile=1.0)
     assert U.dtype == torch.float32 and tuple(U.shape) == (320, 4) and tuple(Vh.shape) == (4, 768)
-    # factors are defined up to sign / rotation inside equal singular values: compare products
-    assert rel_err(U @ Vh, Uo @ Vo) < 1e-3
-    assert abs(max(U.abs().max().item(), Vh.abs().max().item())
-               - max(Uo.abs().max().item(), Vo.abs().max().item())) < 1e-4
+    assert rel_err(U @ Vh, Uo @ Vo) < 1e-4
+    assert rel_err(U.abs(), Uo.abs()) < 1e-3 and rel_err(Vh.abs(), Vo.abs()) < 1e-3
+    # the clamp threshold is the q-quantile of the SIGNED values (cli_svd.py:79-84), so it depends
+    # on the SVD's arbitrary sign convention; pin the property instead: after aligning the signs
+    # to the oracle's, both clamp at the same threshold.
+    sign = torch.sign((U.cpu() * Uo).sum(0))
+    sign[sign == 0] = 1
+    Us, Vs = U.cpu() * sign, Vh.cpu() * sign[:, None]
+    hi = torch.quantile(torch.cat([Us.flatten(), Vs.flatten()]), 0.99)
+    Uc, Vc = O.svd_distill_matrix(delta, rank=4, clamp_quantile=0.99)
+    assert rel_err(Us.clamp(-hi, hi), Uc) < 1e-3 and rel_err(Vs.clamp(-hi, hi), Vc) < 1e-3
+    U2, V2 = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=0.99)
+    own_hi = torch.quantile(torch.cat([U.flatten(), Vh.flatten()]), 0.99).item()
+    assert abs(max(U2.abs().max().item(), V2.abs().max().item()) - own_hi) < 1e-6
