@@ -26,16 +26,16 @@ int tc_pick_bn(int Nout);
 int tc_smem_bytes(int BN, int* stages_out);
 unsigned int tc_read_watchdog();
 template <typename TIO>
-cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                      const TcParams&, int, int, cudaStream_t);
+cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const TcParams&,
+                      int, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, void*, void*, int, int, int, int, cudaStream_t);
 template <typename TIO>
 cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
                         const void*, long long, long long, const void*, long long, long long, int,
                         float, void*, long long, void*, long long, int, int, int, cudaStream_t);
 template <typename T>
-cudaError_t launch_grad_reduce(const void*, long long, const void*, int, float, float*, long long,
-                               long long, float*, long long, int, cudaStream_t);
+cudaError_t launch_lora_grads(const void*, const void*, const void*, const void*, float, float*,
+                              float*, float*, float*, long long, int, int, int, cudaStream_t);
 int grad_reduce_splits(long long M, int C, int esize);
 template <typename TW, typename TL, int MODE>
 cudaError_t launch_merge(const void*, void*, const void*, const void*, float, int, int, int,
@@ -135,7 +135,8 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 // can the tcgen05 path take this problem?  (writes the reason to the error slot if not)
 static bool tc_applicable(const void* X, long long ldx, const void* W, long long ldw, int w_layout,
-                          const void* Y, long long ldy, int r, int io_dtype) {
+                          const void* Y, long long ldy, int r, int io_dtype, int Nout = 0) {
+  if (Nout % 8) { set_error("tc path needs Nout %% 8 == 0"); return false; }
   if (io_dtype == B200LORA_F32) { set_error("tc path needs 16-bit io"); return false; }
   if (w_layout != B200LORA_W_NK) { set_error("tc path needs W as [Nout,Kc]"); return false; }
   if (r < 1 || r > 16) { set_error("tc path needs 1 <= r <= 16"); return false; }
@@ -166,12 +167,13 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, co
   p.S1 = S1_pack; p.s1_rs = Kc; p.s1_cs = 1;
   p.S2 = S2; p.s2_rs = s2_rs; p.s2_cs = s2_cs;
   p.ab_dtype = ab_dtype; p.bias = bias; p.bias_dtype = bias_dtype; p.T_out = T_out;
+  p.Y = Y; p.ldy = ldy;
   const unsigned fmt = io_dtype == B200LORA_BF16 ? 1u : 0u;
   // kind::f16 idesc: D=f32 (1<<4), A/B format, N>>3 at bit 17, M>>4 at bit 24
   p.idesc_main = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)(p.BN + 16) >> 3) << 17) | ((128u >> 4) << 24);
   p.idesc_tail = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)p.BN >> 3) << 17) | ((128u >> 4) << 24);
 
-  CUtensorMap tmX, tmW, tmS, tmY;
+  CUtensorMap tmX, tmW, tmS;
   int rc;
   if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
@@ -179,12 +181,11 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, co
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmS, S1_pack, 16, (uint64_t)Kc, (uint64_t)Kc, 16, 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
-  if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
-                     CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+
   DevInfo di = dev_info();
   cudaError_t e = io_dtype == B200LORA_BF16
-                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmS, tmY, p, smem, di.sms, stream)
-                      : launch_tc<__half>(tmX, tmW, tmS, tmY, p, smem, di.sms, stream);
+                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmS, p, smem, di.sms, stream)
+                      : launch_tc<__half>(tmX, tmW, tmS, p, smem, di.sms, stream);
   if (e != cudaSuccess) {
     set_error("tc launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
@@ -262,7 +263,7 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
     set_error("leading dimension smaller than the row length"); return B200LORA_E_SHAPE;
   }
   if (impl == B200LORA_IMPL_TC || impl == B200LORA_IMPL_AUTO) {
-    bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype);
+    bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype, Nout);
     if (ok && (!S1_pack || !aligned16(S1_pack) || (Kc % 8))) {
       set_error("tc path needs the packed rank rows (b200lora_pack_lora) 16-byte aligned");
       ok = false;
@@ -342,12 +343,7 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
     partB = partA + (int64_t)grad_reduce_splits(M, K, dtype_size(io_dtype)) * K * RP;
   }
   cudaError_t e = cudaSuccess;
-#define RUN(T_)                                                                                  \
-  do {                                                                                           \
-    if (dB) e = launch_grad_reduce<T_>(dY, N, T, r, scale, dB, /*cs=*/r, /*js=*/1, partB, M, N, stream); \
-    if (e == cudaSuccess && dA)                                                                  \
-      e = launch_grad_reduce<T_>(X, K, dT, r, scale, dA, /*cs=*/1, /*js=*/K, partA, M, K, stream); \
-  } while (0)
+#define RUN(T_) e = launch_lora_grads<T_>(dY, X, T, dT, scale, dA, dB, partA, partB, M, K, N, r, stream)
   if (io_dtype == B200LORA_F32) RUN(float);
   else if (io_dtype == B200LORA_F16) RUN(__half);
   else RUN(__nv_bfloat16);

@@ -47,6 +47,7 @@ struct TcParams {
   int ab_dtype;
   const void* bias; int bias_dtype;
   void* T_out;
+  void* Y; long long ldy;
   unsigned idesc_main, idesc_tail;
 };
 
