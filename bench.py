@@ -1,0 +1,407 @@
+"""bench.py — LoRA-UNet training throughput (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference algorithm on the host cores
+
+Workload (BASELINE.json configs[1]): SD-1.5-shaped UNet (random init, synthetic latents), LoRA r=4
+on CrossAttention to_q/to_k/to_v/to_out (128 layers), 64x64 latents, bf16 autocast over fp32
+masters (the reference's `--mixed_precision bf16` mode), batch 8 per GPU, fwd + bwd + global-norm
+clip + AdamW.  A "step" is one such training step on one batch; data-parallel over N GPUs with the
+bucketed LoRA-gradient all-reduce of diffusion_finetuning_b200.dp (weak scaling).
+
+One JSON line on stdout (rank 0).  `value` = samples/s with the batch already in HBM; `e2e` = the
+same through the public API with the batch in pinned HOST memory (H2D inside the timed region) and
+the loss read back every step; `roofline` = the fused tcgen05 LoRA GEMM kernel (forward and
+backward-dX launches), algorithmic FLOPs / CUDA-event time measured live around every launch of
+the timed region; `cpu_baseline` = the oracle's restatement of the reference layer inside the same
+UNet on the host cores (bounded sample: batch 1).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.nn.functional as F  # noqa: E402
+
+METRIC = "LoRA-UNet train samples/sec"
+UNIT = "samples/s"
+ATTN_TARGETS = {"CrossAttention", "Attention"}
+WORKLOAD = "sd15_unet_lora_r4_attn_qkvo_64x64_bf16_b8"
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"tf_burst": p["bf16_tflops"], "tf_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "hbm": p["hbm_gbs"], "src": "measured"}
+    return {"tf_burst": 1590.0, "tf_sustained": 1400.0, "hbm": 6650.0, "src": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampled DURING the timed region
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# live per-launch timing of the hot-path kernels (installed as ops.PROFILER)
+# ------------------------------------------------------------------------------------------------
+class LaunchProfiler:
+    def __init__(self):
+        self.recs = []
+        self.cur = None
+
+    def begin(self, kind, M, K, N, r, esize):
+        a = torch.cuda.Event(enable_timing=True)
+        a.record()
+        self.cur = (kind, M, K, N, r, esize, a)
+
+    def end(self):
+        b = torch.cuda.Event(enable_timing=True)
+        b.record()
+        self.recs.append(self.cur + (b,))
+
+    @staticmethod
+    def work(kind, M, K, N, r, e):
+        """ALGORITHMIC flops / HBM bytes per launch."""
+        if kind == "fwd":      # Y = X W0^T + b + s (X A^T) B^T ; T written for the backward
+            return 2.0 * M * K * N + 2.0 * M * r * (K + N), e * (M * K + N * K + M * N + r * (K + N) + M * r)
+        if kind == "bwd_dx":   # dX = dY W0 + s (dY B) A ; dT written for the reductions
+            return 2.0 * M * K * N + 2.0 * M * r * (K + N), e * (M * N + N * K + M * K + r * (K + N) + M * r)
+        if kind == "grads":    # dA, dB token reductions: re-read X and dY once
+            return 2.0 * M * r * (K + N), e * (M * K + M * N + 2 * M * r) + 4 * r * (K + N)
+        return 0.0, 0.0
+
+    def summary(self):
+        out = {}
+        for kind, M, K, N, r, e, a, b in self.recs:
+            ms = a.elapsed_time(b)
+            fl, by = self.work(kind, M, K, N, r, e)
+            s = out.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            s["launches"] += 1
+            s["ms"] += ms
+            s["flops"] += fl
+            s["bytes"] += by
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# the training job
+# ------------------------------------------------------------------------------------------------
+def make_batches(n, batch, res, seed, device, pin=False):
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n):
+        b = {"latents": torch.randn(batch, 4, res, res, generator=g),
+             "t": torch.randint(0, 1000, (batch,), generator=g),
+             "ctx": torch.randn(batch, 77, 768, generator=g),
+             "target": torch.randn(batch, 4, res, res, generator=g)}
+        if device is not None:
+            b = {k: v.to(device) for k, v in b.items()}
+        elif pin:
+            b = {k: v.pin_memory() for k, v in b.items()}
+        out.append(b)
+    return out
+
+
+class Trainer:
+    """The public API a user of the reference calls, end to end: inject_trainable_lora ->
+    optimizer over the returned parameter generators -> fwd/bwd/clip/step
+    (train_lora_dreambooth.py:595-676, 816-888)."""
+
+    def __init__(self, device, rank_r, autocast=True):
+        import itertools
+        import diffusion_finetuning_b200 as L
+        from diffusion_finetuning_b200 import dp
+        from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
+        torch.manual_seed(0)                      # same frozen base on every rank
+        self.unet = UNet2DConditionModel().to(device)
+        self.unet.requires_grad_(False)
+        params, names = L.inject_trainable_lora(self.unet, ATTN_TARGETS, r=rank_r)
+        self.n_layers = len(names)
+        g = torch.Generator(device="cpu").manual_seed(1)
+        with torch.no_grad():                     # non-zero up so every gradient is live
+            for m in self.unet.modules():
+                if isinstance(m, L.LoraInjectedLinear):
+                    m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
+        self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
+        self.arena.broadcast_params(0)
+        self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True)
+        self.device = device
+        self.autocast = autocast
+
+    def step(self, b):
+        self.arena.zero()
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.autocast):
+            pred = self.unet(b["latents"], b["t"], b["ctx"])
+        loss = F.mse_loss(pred.float(), b["target"].float(), reduction="mean")
+        loss.backward()
+        self.arena.finish()
+        self.arena.clip_grad_norm_(1.0)
+        self.opt.step()
+        return loss
+
+    def step_from_host(self, hb):
+        b = {k: v.to(self.device, non_blocking=True) for k, v in hb.items()}
+        return self.step(b).item()              # D2H read of the loss every step
+
+
+def timed(fn, steps, dist_on, device):
+    """K steps between barrier+synchronize, CUDA events, MAX over ranks -> seconds."""
+    import torch.distributed as dist
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        fn(i)
+    b.record()
+    torch.cuda.synchronize(device)
+    if dist_on:
+        dist.barrier()
+    ms = torch.tensor([a.elapsed_time(b)], device=device)
+    if dist_on:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return ms.item() * 1e-3
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU leg: the reference algorithm (oracle restatement of lora.py:32-50, 137-183) on host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_leg(steps, warmup, batch, res, rank_r):
+    import itertools
+    from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
+    from oracle import lora_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    unet = UNet2DConditionModel()
+    unet.requires_grad_(False)
+    layers = O.inject(unet, ATTN_TARGETS, r=rank_r)
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for m in layers:
+            m.lora_up.weight.copy_(torch.randn(m.lora_up.weight.shape, generator=g) * 0.02)
+    params = list(itertools.chain(*[[m.lora_up.weight, m.lora_down.weight] for m in layers]))
+    opt = torch.optim.AdamW(params, lr=1e-4)
+    batches = make_batches(2, batch, res, 1234, None)
+
+    def step(b):
+        opt.zero_grad(set_to_none=True)
+        pred = unet(b["latents"], b["t"], b["ctx"])
+        loss = F.mse_loss(pred.float(), b["target"].float())
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 1.0)
+        opt.step()
+        return loss.item()
+
+    for i in range(warmup):
+        step(batches[i % 2])
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(batches[i % 2])
+    dt = time.perf_counter() - t0
+    return {"value": batch * steps / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} steps of batch {batch} (1/8 of the per-GPU batch) at {res}x{res} latents, fp32, "
+                      f"oracle/lora_oracle.py layers inside the same UNet, {len(layers)} LoRA layers",
+            "ms_per_step": dt / steps * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cb = cpu_leg(args.steps, max(1, min(args.warmup, 2)), 1, args.res, args.rank)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config_dict(args, 1),
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def config_dict(args, batch):
+    return {"workload": WORKLOAD, "unet": "SD-1.5 shape (320,640,1280,1280), 2 layers/block, ctx 77x768",
+            "lora": f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out", "latents": f"{args.res}x{args.res}",
+            "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
+            "optimizer": "AdamW lr 1e-4, clip 1.0",
+            "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--res", type=int, default=64)
+    ap.add_argument("--rank", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--breakdown", default=None, help="write the per-kernel breakdown JSON here")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the b200lora kernels are the only compute path")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    dist_on = world > 1
+    if dist_on:
+        dist.init_process_group("nccl", device_id=device)
+    import __graft_entry__ as entry
+    if rank == 0:
+        entry.build()
+    if dist_on:
+        dist.barrier()
+    from diffusion_finetuning_b200 import _native as nat
+    from diffusion_finetuning_b200 import ops
+    nat.lib()
+
+    tr = Trainer(device, args.rank)
+    pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
+    host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
+    for i in range(args.warmup):
+        tr.step(pool[i % 4])
+    tr.step_from_host(host_pool[0])
+    torch.cuda.synchronize(device)
+
+    # ---- timed region 1: batch resident in HBM, per-launch events live ----
+    prof = LaunchProfiler()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ops.PROFILER = prof
+    l0 = nat.LAUNCHES
+    t_dev = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
+    launches = nat.LAUNCHES - l0
+    ops.PROFILER = None
+    # ---- timed region 2: end to end from pinned host memory, loss read back every step ----
+    t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
+    clk = clocks.stop() if rank == 0 else None
+
+    if rank != 0:
+        if dist_on:
+            dist.destroy_process_group()
+        return 0
+
+    pk = peaks()
+    summ = prof.summary()
+    gemm = {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0}
+    for k in ("fwd", "bwd_dx"):
+        for f in gemm:
+            gemm[f] += summ.get(k, {}).get(f, 0)
+    step_ms = t_dev / args.steps * 1e3
+    ach_tf = gemm["flops"] / (gemm["ms"] * 1e-3) / 1e12 if gemm["ms"] else 0.0
+    roofline = {"kernel": "lora_gemm_tc_kernel (fused LoRA linear forward + backward-dX launches)",
+                "bound": "tensor", "achieved": ach_tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                "frac": ach_tf / pk["tf_sustained"], "peak_source": pk["src"] + " (sustained bf16)",
+                "traffic": None,
+                "launches_per_step": gemm["launches"] / args.steps,
+                "avg_launch_us": gemm["ms"] * 1e3 / max(1, gemm["launches"]),
+                "share_of_step": gemm["ms"] / args.steps / step_ms,
+                "achieved_hbm_gbs": gemm["bytes"] / (gemm["ms"] * 1e-3) / 1e9 if gemm["ms"] else 0.0}
+    if "grads" in summ:
+        s = summ["grads"]
+        roofline["grads_kernel"] = {"bound": "hbm", "achieved": s["bytes"] / (s["ms"] * 1e-3) / 1e9, "peak": pk["hbm"],
+                                    "unit": "GB/s", "frac": s["bytes"] / (s["ms"] * 1e-3) / 1e9 / pk["hbm"],
+                                    "share_of_step": s["ms"] / args.steps / step_ms}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get("lora_gemm_tc_kernel_bytes_per_launch")
+        except (ValueError, OSError):
+            pass
+    bytes_in = sum(v.numel() * v.element_size() for v in host_pool[0].values())
+    samples = args.batch * world * args.steps
+    line = {"metric": METRIC, "value": samples / t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config_dict(args, args.batch),
+            "e2e": {"value": samples / t_e2e, "unit": UNIT, "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 4},
+            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
+            "grad_allreduce": {"payload_bytes": tr.arena.payload_bytes, "buckets": len(tr.arena.buckets)},
+            "lora_layers": tr.n_layers}
+    if args.breakdown:
+        os.makedirs(os.path.dirname(os.path.abspath(args.breakdown)), exist_ok=True)
+        json.dump({"per_kind": summ, "step_ms": step_ms, "steps": args.steps}, open(args.breakdown, "w"), indent=1)
+    if world == 1 and not args.no_cpu_baseline:
+        del tr, pool
+        torch.cuda.empty_cache()
+        cb = cpu_leg(3, 1, 1, args.res, args.rank)
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line), flush=True)
+    if dist_on:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

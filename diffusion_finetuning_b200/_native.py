@@ -77,10 +77,17 @@ def dtype_code(dt):
         raise B200LoraError(f"unsupported dtype {dt}; b200lora handles fp32/fp16/bf16") from None
 
 
+# number of successful C-ABI kernel launches since import (every entry point that computes is
+# exactly one kernel launch); bench.py reports the delta over its timed region as `gpu_launches`
+LAUNCHES = 0
+
+
 def check(rc, what):
+    global LAUNCHES
     if rc != 0:
         msg = lib().b200lora_last_error().decode(errors="replace")
         raise B200LoraError(f"{what} failed with code {rc}: {msg}")
+    LAUNCHES += 1
 
 
 def stream_ptr(device):

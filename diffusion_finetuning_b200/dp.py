@@ -1,0 +1,240 @@
+"""Data-parallel exchange step of LoRA training: one flat fp32 gradient arena, split into a few
+buckets that are all-reduced (averaged) over NCCL on a side stream WHILE the rest of the backward
+runs.
+
+What it replaces in the reference: `accelerator.prepare(unet, ...)` + `accelerator.backward(loss)`
+(training_scripts/train_lora_dreambooth.py:751-757, 877), i.e. torch DDP over the trainable
+parameters only.  The base model is frozen (train_lora_dreambooth.py:595), so the payload is the
+LoRA A/B gradients: 3.2 MB (attention, r=4) to 20 MB (default targets, r=16) in fp32.  Stock DDP
+puts all of it in ONE 25 MB bucket that fires after the last gradient, so nothing overlaps.  Here:
+
+  * every injected layer owns two slices of ONE flat fp32 arena, laid out in reverse module order
+    (the order the backward produces them); the dA/dB reduction kernel ADDS straight into those
+    slices (ops.GradSink), so no per-layer zero-fill / cast / accumulate kernels run;
+  * the arena is cut into buckets of >= `bucket_bytes`; a bucket's all-reduce is enqueued on a side
+    stream the moment its last slice is final, gated by an event on the compute stream;
+  * `finish()` joins the side stream, fires whatever did not fire (unused layers), and leaves
+    `p.grad` of every parameter pointing at the averaged values, ready for any torch optimizer.
+
+The path shards by batch only: there is no other collective.  With world_size 1
+(or no process group) the arena still removes the per-layer gradient plumbing; no collective runs.
+Works on CPU tensors with the `gloo` backend (tests), where the "side stream" is the backend's
+own worker thread.
+"""
+from typing import Iterable, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import ops
+from .lora import LoraInjectedConv2d, LoraInjectedLinear
+
+
+class _Bucket:
+    __slots__ = ("lo", "hi", "expected", "pending", "work", "fired")
+
+    def __init__(self, lo):
+        self.lo, self.hi = lo, lo
+        self.expected = 0      # parameters whose slices live in this bucket
+        self.pending = 0
+        self.work = None
+        self.fired = False
+
+
+class LoraGradArena:
+    """Flat gradient arena + bucketed, overlapped all-reduce for the trainable LoRA parameters.
+
+    Usage per step:
+        arena.zero()                    # instead of optimizer.zero_grad()
+        loss.backward()                 # buckets fire as their layers finish
+        arena.finish()                  # join; p.grad = averaged gradients
+        arena.clip_grad_norm_(1.0)      # optional, one pass over the arena
+        optimizer.step()
+    """
+
+    def __init__(self, model: nn.Module, extra_params: Iterable[nn.Parameter] = (),
+                 bucket_bytes: int = 1 << 20, process_group=None, average: bool = True):
+        self.group = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.average = average
+        layers = [m for m in model.modules() if isinstance(m, (LoraInjectedLinear, LoraInjectedConv2d))]
+        if not layers and not list(extra_params):
+            raise ValueError("No lora injected.")
+        # (param, owning Linear layer or None), in the order the backward finishes them
+        entries = []
+        for layer in reversed(layers):
+            entries.append((layer.lora_up.weight, layer))
+            entries.append((layer.lora_down.weight, layer))
+        for p in extra_params:
+            entries.append((p, None))
+        entries = [(p, l) for p, l in entries if p.requires_grad]
+        self.params: List[nn.Parameter] = [p for p, _ in entries]
+        if not self.params:
+            raise ValueError("no trainable LoRA parameter")
+        dev = self.params[0].device
+        self.device = dev
+        total = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self._lowp = {}          # dtype -> flat low-precision copy for non-fp32 parameters
+        self.buckets: List[_Bucket] = []
+        self._slot = {}          # id(param) -> (offset, numel, bucket index)
+        cap = max(1, bucket_bytes // 4)
+        b = _Bucket(0)
+        off = 0
+        for p, _ in entries:
+            if b.hi - b.lo >= cap:
+                self.buckets.append(b)
+                b = _Bucket(off)
+            self._slot[id(p)] = (off, p.numel(), len(self.buckets))
+            off += p.numel()
+            b.hi = off
+            b.expected += 1
+        self.buckets.append(b)
+        self._hooks = []
+        self._sync = True
+        self._comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        for p, layer in entries:
+            o, n, bi = self._slot[id(p)]
+            view = self.flat[o:o + n].view_as(p)
+            if p.dtype == torch.float32:
+                p.grad = view
+            else:
+                lp = self._lowp.get(p.dtype)
+                if lp is None:
+                    lp = self._lowp[p.dtype] = torch.zeros(total, dtype=p.dtype, device=dev)
+                p.grad = lp[o:o + n].view_as(p)
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(bi)))
+        for layer in layers:
+            if isinstance(layer, LoraInjectedLinear) and id(layer.lora_up.weight) in self._slot \
+                    and id(layer.lora_down.weight) in self._slot:
+                oB, nB, bB = self._slot[id(layer.lora_up.weight)]
+                oA, nA, bA = self._slot[id(layer.lora_down.weight)]
+                layer._grad_sink = ops.GradSink(
+                    self.flat[oA:oA + nA].view_as(layer.lora_down.weight),
+                    self.flat[oB:oB + nB].view_as(layer.lora_up.weight),
+                    self._make_sink_ready(bA, bB))
+        self._layers = layers
+        self.zero()
+
+    # ------------------------------------------------------------------ bookkeeping
+    def _make_hook(self, bi):
+        def hook(param):
+            # autograd accumulated into p.grad (a view of the arena for fp32 parameters; for
+            # low-precision parameters the value is folded into the fp32 arena here)
+            if param.dtype != torch.float32:
+                o, n, _ = self._slot[id(param)]
+                self.flat[o:o + n].add_(param.grad.reshape(-1).float())
+                param.grad.zero_()      # folded; finish() writes the reduced value back
+            self._ready(bi)
+        return hook
+
+    def _make_sink_ready(self, bA, bB):
+        def ready():
+            self._ready(bA)
+            self._ready(bB)
+        return ready
+
+    def _ready(self, bi):
+        b = self.buckets[bi]
+        b.pending -= 1
+        if b.pending == 0 and self._sync:
+            self._fire(b)
+
+    def _fire(self, b):
+        if b.fired:
+            return
+        b.fired = True
+        if self.world == 1:
+            return
+        view = self.flat[b.lo:b.hi]
+        nccl = self._comm is not None
+        op = dist.ReduceOp.AVG if (nccl and self.average) else dist.ReduceOp.SUM
+        if nccl:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._comm):
+                self._comm.wait_event(ev)
+                b.work = dist.all_reduce(view, op=op, group=self.group, async_op=True)
+        else:
+            b.work = dist.all_reduce(view, op=op, group=self.group, async_op=True)
+
+    # ------------------------------------------------------------------ public
+    def zero(self):
+        """Zero the arena and re-arm the buckets (replaces optimizer.zero_grad())."""
+        self.flat.zero_()
+        for lp in self._lowp.values():
+            lp.zero_()
+        for b in self.buckets:
+            b.pending, b.work, b.fired = b.expected, None, False
+
+    class _NoSync:
+        def __init__(self, arena):
+            self.arena = arena
+
+        def __enter__(self):
+            self.arena._sync = False
+
+        def __exit__(self, *exc):
+            self.arena._sync = True
+            for b in self.arena.buckets:      # re-arm: the next backward is the one that fires
+                b.pending = b.expected
+            return False
+
+    def no_sync(self):
+        """Gradient accumulation: backward passes inside this context only accumulate; the
+        all-reduce happens at `finish()` (accelerate's `accumulate`, train_lora_dreambooth.py:817)."""
+        return LoraGradArena._NoSync(self)
+
+    def finish(self):
+        """Join the exchange: every bucket reduced, gradients averaged, `p.grad` final."""
+        for b in self.buckets:
+            if not b.fired:
+                self._fire(b)
+        for b in self.buckets:
+            if b.work is not None:
+                b.work.wait()
+                b.work = None
+        if self._comm is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._comm)
+        if self.world > 1 and self.average and self._comm is None:
+            self.flat.mul_(1.0 / self.world)        # gloo has no AVG
+        for dt, lp in self._lowp.items():
+            lp.copy_(self.flat)
+
+    def clip_grad_norm_(self, max_norm: float):
+        """Global L2 clip over the arena (clip_grad_norm_ over all LoRA parameters,
+        train_lora_dreambooth.py:878-884 / cli_lora_pti.py:448-450) in one pass."""
+        total = torch.linalg.vector_norm(self.flat)
+        coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+        self.flat.mul_(coef)
+        for lp in self._lowp.values():
+            lp.mul_(coef.to(lp.dtype))
+        return total
+
+    def broadcast_params(self, src: int = 0):
+        """Replicas must start identical: lora_down is random-initialised per process
+        (lora.py:46), so rank `src`'s values are broadcast once (what DDP does at wrap time)."""
+        if self.world == 1:
+            return
+        with torch.no_grad():
+            flat = torch.cat([p.detach().reshape(-1).float() for p in self.params])
+            dist.broadcast(flat, src=src, group=self.group)
+            off = 0
+            for p in self.params:
+                n = p.numel()
+                p.copy_(flat[off:off + n].view_as(p).to(p.dtype))
+                off += n
+
+    @property
+    def payload_bytes(self):
+        return self.flat.numel() * 4
+
+    def detach(self):
+        """Undo the wiring (hooks and sinks); gradients stay where they are."""
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        for layer in self._layers:
+            if isinstance(layer, LoraInjectedLinear):
+                layer._grad_sink = None

@@ -67,6 +67,7 @@ class LoraInjectedLinear(nn.Module):
         nn.init.normal_(self.lora_down.weight, std=1 / r)   # lora.py:46
         nn.init.zeros_(self.lora_up.weight)                 # lora.py:47
         self._base_cache = ops.BaseWeightCache()
+        self._grad_sink = None      # set by dp.LoraGradArena: dA/dB land in a flat fp32 arena
 
     def _down_weight(self):
         """lora_down weight with a diagonal selector folded in (selector(T) = T·diag(d))."""
@@ -87,8 +88,9 @@ class LoraInjectedLinear(nn.Module):
                                    B.detach(), 0.0, cache=self._base_cache)
             branch = ops.lora_linear(input, torch.zeros_like(self.linear.weight), None, A, B, 1.0)
             return base + self.dropout(branch) * self.scale
+        sink = self._grad_sink if A is self.lora_down.weight else None
         return ops.lora_linear(input, self.linear.weight, self.linear.bias, A, B, self.scale,
-                               cache=self._base_cache)
+                               cache=self._base_cache, sink=sink)
 
     def realize_as_lora(self):
         return self.lora_up.weight.data * self.scale, self.lora_down.weight.data

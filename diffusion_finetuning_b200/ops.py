@@ -111,11 +111,45 @@ def _compute_dtype(x, w0):
     return x.dtype
 
 
+# Optional launch profiler (bench.py installs one): an object with begin(kind, M, K, N, r, esize)
+# and end(), called on either side of every hot-path launch on the launching stream.
+PROFILER = None
+
+
+class _Prof:
+    """`with _Prof(kind, ...)`: brackets one launch with the installed profiler, if any."""
+    __slots__ = ("args", "p")
+
+    def __init__(self, *args):
+        self.args = args
+        self.p = PROFILER
+
+    def __enter__(self):
+        if self.p is not None:
+            self.p.begin(*self.args)
+
+    def __exit__(self, *exc):
+        if self.p is not None:
+            self.p.end()
+        return False
+
+
+class GradSink:
+    """Where the gradient reductions of one injected layer land: fp32 slices of a flat gradient
+    arena (dp.LoraGradArena).  With a sink the dA/dB kernel ADDS straight into the arena (no
+    zero-fill, cast or autograd accumulate launches) and `ready()` tells the arena that this
+    layer's slice is final for the step, which is what fires a bucket's all-reduce."""
+    __slots__ = ("dA", "dB", "ready")
+
+    def __init__(self, dA, dB, ready):
+        self.dA, self.dB, self.ready = dA, dB, ready
+
+
 class _LoraLinearFn(torch.autograd.Function):
     """y = x·W0ᵀ + b + s·(x·Aᵀ)·Bᵀ as ONE kernel; backward = fused dX kernel + token reductions."""
 
     @staticmethod
-    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic):
+    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic, sink=None):
         nat.require_cuda(x, "LoraInjectedLinear.forward")
         for name, t in (("linear.weight", w0), ("lora_down.weight", A), ("lora_up.weight", B)):
             if t.device != x.device:
@@ -151,24 +185,25 @@ class _LoraLinearFn(torch.autograd.Function):
         if use_tc and M > 0:
             a_pack, bt_pack = cache.lora_pack(A, B, cdt)
         if M > 0:
-            with torch.cuda.device(x.device):
+            with torch.cuda.device(x.device), _Prof("fwd", M, K, N, r, x2.element_size()):
                 rc = lib.b200lora_linear_fwd(
                     nat.ptr(x2), nat.ptr(w), nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
                     nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype), nat.ptr(a_pack), float(scale),
                     nat.ptr(y), nat.ptr(T), M, K, N, r, nat.dtype_code(cdt),
                     nat.IMPL_TC if use_tc else nat.IMPL_SIMT, nat.stream_ptr(x.device))
-            nat.check(rc, "b200lora_linear_fwd")
+                nat.check(rc, "b200lora_linear_fwd")
         if need_grad:
             ctx.save_for_backward(x2, T, A, B, w0, w)
             ctx.meta = (lead, M, K, N, r, float(scale), cdt, use_tc, cache, bool(deterministic),
-                        x.dtype, bias is not None, bt_pack)
+                        x.dtype, bias is not None, bt_pack, sink)
         return y.reshape(*lead, N)
 
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, dy):
         x2, T, A, B, w0, w = ctx.saved_tensors
-        lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias, bt_pack = ctx.meta
+        (lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias, bt_pack,
+         sink) = ctx.meta
         lib = nat.lib()
         dev = dy.device
         dy2 = dy.reshape(-1, N)
@@ -192,6 +227,9 @@ class _LoraLinearFn(torch.autograd.Function):
                 dT = torch.empty((M, r), dtype=cdt, device=dev)
                 if use_tc:
                     wt = cache.get(w0, "t", cdt)
+                prof = _Prof("bwd_dx", M, K, N, r, dy2.element_size())
+                prof.__enter__()
+                if use_tc:
                     rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(wt), nat.W_NK, nat.ptr(Ac),
                                                     nat.ptr(Bc), ab_code, nat.ptr(bt_pack), scale, nat.ptr(dx),
                                                     nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_TC, stream)
@@ -200,23 +238,32 @@ class _LoraLinearFn(torch.autograd.Function):
                                                     nat.ptr(Bc), ab_code, None, scale, nat.ptr(dx),
                                                     nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_SIMT, stream)
                 nat.check(rc, "b200lora_linear_bwd_dx")
+                prof.__exit__()
             dA = dB = None
+            use_sink = sink is not None and need_A and need_B
             if (need_A or need_B):
-                dA32 = torch.zeros((r, K), dtype=torch.float32, device=dev) if need_A else None
-                dB32 = torch.zeros((N, r), dtype=torch.float32, device=dev) if need_B else None
+                if use_sink:
+                    dA32, dB32 = sink.dA, sink.dB      # fp32 arena slices; the kernel adds into them
+                else:
+                    dA32 = torch.zeros((r, K), dtype=torch.float32, device=dev) if need_A else None
+                    dB32 = torch.zeros((N, r), dtype=torch.float32, device=dev) if need_B else None
                 if M > 0:
                     ws = None
                     ws_bytes = 0
                     if deterministic:
                         ws_bytes = int(lib.b200lora_lora_grads_workspace(M, K, N, r))
                         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-                    rc = lib.b200lora_lora_grads(nat.ptr(dy2), nat.ptr(x2), nat.ptr(T), nat.ptr(dT),
-                                                 scale, nat.ptr(dA32), nat.ptr(dB32), M, K, N, r,
-                                                 io_code, 1 if deterministic else 0, nat.ptr(ws),
-                                                 ws_bytes, stream)
-                    nat.check(rc, "b200lora_lora_grads")
-                dA = dA32.to(A.dtype) if need_A else None
-                dB = dB32.to(B.dtype) if need_B else None
+                    with _Prof("grads", M, K, N, r, dy2.element_size()):
+                        rc = lib.b200lora_lora_grads(nat.ptr(dy2), nat.ptr(x2), nat.ptr(T), nat.ptr(dT),
+                                                     scale, nat.ptr(dA32), nat.ptr(dB32), M, K, N, r,
+                                                     io_code, 1 if deterministic else 0, nat.ptr(ws),
+                                                     ws_bytes, stream)
+                        nat.check(rc, "b200lora_lora_grads")
+                if use_sink:
+                    sink.ready()                       # grads live in the arena, not in autograd
+                else:
+                    dA = dA32.to(A.dtype) if need_A else None
+                    dB = dB32.to(B.dtype) if need_B else None
         dW = db = None
         if need_w:
             # Unfrozen base: never the case in the reference's flows (unet.requires_grad_(False),
@@ -230,16 +277,19 @@ class _LoraLinearFn(torch.autograd.Function):
                 dx = dx.to(x_dtype)
         else:
             dx = None
-        return dx, dW, db, dA, dB, None, None, None, None
+        return dx, dW, db, dA, dB, None, None, None, None, None
 
 
-def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None):
-    """Functional form of LoraInjectedLinear.forward (reference lora.py:49-50)."""
+def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None,
+                sink=None):
+    """Functional form of LoraInjectedLinear.forward (reference lora.py:49-50).
+    `sink` (GradSink, optional) routes dA/dB straight into a flat gradient arena."""
     if impl is None:
         impl = _impl_from_env()
     if deterministic is None:
         deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
-    return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic)
+    return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic,
+                               sink)
 
 
 # --------------------------------------------------------------------------------------------
@@ -301,16 +351,20 @@ def lora_abs_mean(up, down):
 def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99):
     """Rank-r factorisation of one weight difference (reference cli_svd.py:69-84).
 
-    The SVD stays on cuSOLVER (torch.linalg.svd, economy size: only the top-r triplets are kept,
-    so `full_matrices` of the reference is wasted work); U·diag(S), the symmetric clamp at the
+    The SVD stays on cuSOLVER (torch.linalg.svd driver gesvd, economy size: only the top-r
+    triplets are kept, so `full_matrices` of the reference is wasted work); U·diag(S), the symmetric clamp at the
     `clamp_quantile` quantile of [U, Vh] and the slicing run in the epilogue kernel.
     Returns (U [N,r], Vh [r,K]) fp32 — the `[up, down]` pair the reference saves.
+    `clamp_quantile=None` skips the clamp (not a reference mode; used to test the factorisation,
+    because the clamp threshold depends on the SVD's arbitrary sign convention).
     """
     lib = nat.lib()
     dev = delta.device if delta.is_cuda else _cuda_device()
     with torch.no_grad():
         mat = delta.detach().to(dev).float()
-        U, S, Vh = torch.linalg.svd(mat, full_matrices=False)
+        # driver="gesvd": cuSOLVER's QR-iteration SVD.  torch's default on CUDA is the Jacobi
+        # driver (gesvdj), whose fp32 factors were measured 7e-3 off the LAPACK result on B200.
+        U, S, Vh = torch.linalg.svd(mat, full_matrices=False, driver="gesvd")
         U = U[:, :rank].contiguous()
         S = S[:rank].contiguous()
         Vh = Vh[:rank, :].contiguous()
@@ -319,8 +373,9 @@ def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99):
         with torch.cuda.device(dev):
             rc = lib.b200lora_svd_epilogue(nat.ptr(U), nat.ptr(S), nat.ptr(Vh), -1.0, 1, N, K, rank, stream)
             nat.check(rc, "b200lora_svd_epilogue(scale)")
-            dist = torch.cat([U.flatten(), Vh.flatten()])
-            hi = torch.quantile(dist, clamp_quantile).item()
-            rc = lib.b200lora_svd_epilogue(nat.ptr(U), nat.ptr(S), nat.ptr(Vh), float(hi), 0, N, K, rank, stream)
-            nat.check(rc, "b200lora_svd_epilogue(clamp)")
+            if clamp_quantile is not None:
+                dist = torch.cat([U.flatten(), Vh.flatten()])
+                hi = torch.quantile(dist, clamp_quantile).item()
+                rc = lib.b200lora_svd_epilogue(nat.ptr(U), nat.ptr(S), nat.ptr(Vh), float(hi), 0, N, K, rank, stream)
+                nat.check(rc, "b200lora_svd_epilogue(clamp)")
         return U, Vh

@@ -109,8 +109,10 @@ def test_svd_distill_matches_oracle():
     delta = (up @ down + 1e-4 * torch.randn(320, 768, generator=g)).half()
     # without the clamp the factorisation is unique up to the sign of each singular pair:
     # compare the products (cli_svd.py:69-77)
-    U, Vh = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=1.0)
-    Uo, Vo = O.svd_distill_matrix(delta, rank=4, clamp_quantile=1.0)
+    # (clamp_quantile=1.0 is NOT a no-op: the threshold is the max of the SIGNED values, so a more
+    # negative entry is clamped, and which entries are negative depends on the SVD's signs)
+    U, Vh = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=None)
+    Uo, Vo = O.svd_distill_matrix(delta, rank=4, clamp_quantile=None)
     assert U.dtype == torch.float32 and tuple(U.shape) == (320, 4) and tuple(Vh.shape) == (4, 768)
     assert rel_err(U @ Vh, Uo @ Vo) < 1e-4
     assert rel_err(U.abs(), Uo.abs()) < 1e-3 and rel_err(Vh.abs(), Vo.abs()) < 1e-3
@@ -125,4 +127,5 @@ def test_svd_distill_matches_oracle():
     assert rel_err(Us.clamp(-hi, hi), Uc) < 1e-3 and rel_err(Vs.clamp(-hi, hi), Vc) < 1e-3
     U2, V2 = ops.svd_distill_matrix(delta.to(DEV), rank=4, clamp_quantile=0.99)
     own_hi = torch.quantile(torch.cat([U.flatten(), Vh.flatten()]), 0.99).item()
+    assert own_hi > 0
     assert abs(max(U2.abs().max().item(), V2.abs().max().item()) - own_hi) < 1e-6
