@@ -29,9 +29,10 @@ SIGNATURES = {
     "b200lora_last_error": (ctypes.c_char_p, []),
     "b200lora_tc_supported": (_i32, []),
     "b200lora_lora_gemm": (_i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i32, _vp, _i64, _i64, _vp, _vp,
-                                  _i64, _i64, _i32, _f32, _vp, _i64, _vp, _i64, _i32, _i32, _i32,
-                                  _i32, _i32, _vp]),
-    "b200lora_pack_lora": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+                                  _i64, _i64, _i32, _vp, _f32, _vp, _i64, _vp, _i64, _i32, _i32,
+                                  _i32, _i32, _i32, _vp]),
+    "b200lora_pack_elems": (_i64, [_i32, _i32]),
+    "b200lora_pack_lora": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_linear_fwd": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp, _f32, _vp, _vp, _i64,
                                    _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_linear_bwd_dx": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _vp, _f32, _vp, _vp, _i64,

@@ -24,11 +24,13 @@ void set_error(const char* fmt, ...) {
 // forward declarations of the per-file launchers
 int tc_pick_bn(int Nout);
 int tc_smem_bytes(int BN, int* stages_out);
+void tc_tmem_plan(int BN, int* nst, int* stride);
 unsigned int tc_read_watchdog();
 template <typename TIO>
-cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const TcParams&,
-                      int, int, cudaStream_t);
-cudaError_t launch_pack(const void*, const void*, int, void*, void*, int, int, int, int, cudaStream_t);
+cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                      const CUtensorMap&, const TcParams&, int, int, cudaStream_t);
+cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
+                        int, int, int, int, cudaStream_t);
 template <typename TIO>
 cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
                         const void*, long long, long long, const void*, long long, long long, int,
@@ -149,10 +151,13 @@ static bool tc_applicable(const void* X, long long ldx, const void* W, long long
   return true;
 }
 
-static int run_tc(const void* X, long long ldx, const void* W, long long ldw, const void* bias,
-                  int bias_dtype, const void* S1_pack, const void* S2,
-                  long long s2_rs, long long s2_cs, int ab_dtype, float scale, void* Y,
-                  long long ldy, void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
+// debug timeline target (tools/timeline.py): device buffer of 6*256 int64 and the CTA to trace
+static long long* g_dbg_buf = nullptr;
+static int g_dbg_cta = 0;
+
+static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bool has_bias,
+                  const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
+                  void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
                   cudaStream_t stream) {
   TcParams p;
   memset(&p, 0, sizeof(p));
@@ -163,29 +168,37 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, co
   p.num_k_blk = (Kc + 63) / 64;
   const int smem = tc_smem_bytes(p.BN, &p.stages);
   if (p.stages < 2) { set_error("tc: not enough shared memory for BN=%d", p.BN); return B200LORA_E_SHAPE; }
+  tc_tmem_plan(p.BN, &p.nst, &p.acc_stride);
   p.scale = scale;
-  p.S1 = S1_pack; p.s1_rs = Kc; p.s1_cs = 1;
-  p.S2 = S2; p.s2_rs = s2_rs; p.s2_cs = s2_cs;
-  p.ab_dtype = ab_dtype; p.bias = bias; p.bias_dtype = bias_dtype; p.T_out = T_out;
-  p.Y = Y; p.ldy = ldy;
+  p.has_bias = has_bias ? 1 : 0;
+  p.tail_ksteps = (r + p.has_bias > 16) ? 2 : 1;
+  p.T_out = T_out;
+  p.dbg = g_dbg_buf;
+  p.dbg_cta = g_dbg_cta;
   const unsigned fmt = io_dtype == B200LORA_BF16 ? 1u : 0u;
   // kind::f16 idesc: D=f32 (1<<4), A/B format, N>>3 at bit 17, M>>4 at bit 24
-  p.idesc_main = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)(p.BN + 16) >> 3) << 17) | ((128u >> 4) << 24);
-  p.idesc_tail = (1u << 4) | (fmt << 7) | (fmt << 10) | (((unsigned)p.BN >> 3) << 17) | ((128u >> 4) << 24);
+  const unsigned base = (1u << 4) | (fmt << 7) | (fmt << 10) | ((128u >> 4) << 24);
+  p.idesc_main = base | (((unsigned)p.BN >> 3) << 17);
+  p.idesc_main_t = base | (((unsigned)(p.BN + 16) >> 3) << 17);
+  p.idesc_tail = p.idesc_main;
 
-  CUtensorMap tmX, tmW, tmS;
+  CUtensorMap tmX, tmW, tmS1, tmS2, tmY;
   int rc;
   if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmW, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)p.BN, 64,
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
-  if ((rc = get_tmap(&tmS, S1_pack, 16, (uint64_t)Kc, (uint64_t)Kc, 16, 64, io_dtype,
+  if ((rc = get_tmap(&tmS1, S1_pack, 16, (uint64_t)Kc, (uint64_t)Kc, 16, 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmS2, S2_pack, (uint64_t)Nout, 64, 64, (uint32_t)p.BN, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
 
   DevInfo di = dev_info();
   cudaError_t e = io_dtype == B200LORA_BF16
-                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmS, p, smem, di.sms, stream)
-                      : launch_tc<__half>(tmX, tmW, tmS, p, smem, di.sms, stream);
+                      ? launch_tc<__nv_bfloat16>(tmX, tmW, tmS1, tmS2, tmY, p, smem, di.sms, stream)
+                      : launch_tc<__half>(tmX, tmW, tmS1, tmS2, tmY, p, smem, di.sms, stream);
   if (e != cudaSuccess) {
     set_error("tc launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
@@ -229,17 +242,33 @@ extern "C" int b200lora_tc_supported(void) {
 // diagnostic: non-zero if the tensor-core kernel's watchdog fired (site<<16 | block)
 extern "C" unsigned int b200lora_watchdog_code(void) { return tc_read_watchdog(); }
 
-extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, void* A_pack,
-                                  void* Bt_pack, int K, int N, int r, int io_dtype,
+// diagnostic, not part of the drop-in surface: trace CTA `cta` of the next tcgen05 launches
+extern "C" void b200lora_debug_timeline(void* buf, int cta) {
+  g_dbg_buf = reinterpret_cast<long long*>(buf);
+  g_dbg_cta = cta;
+}
+
+extern "C" int64_t b200lora_pack_elems(int K, int N) { return 80ll * ((int64_t)K + N); }
+
+extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, const void* bias,
+                                  int bias_dtype, void* pack, int K, int N, int r, int io_dtype,
                                   b200lora_stream_t stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   g_err[0] = 0;
-  if (!A || !B || !A_pack || !Bt_pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
-  if (!valid_dtype(ab_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
+  if (!A || !B || !pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype)) ||
+      (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
     set_error("pack_lora: io dtype must be bf16/fp16"); return B200LORA_E_DTYPE;
   }
   if (K < 1 || N < 1 || r < 1 || r > 16) { set_error("pack_lora: needs 1 <= r <= 16"); return B200LORA_E_SHAPE; }
-  cudaError_t e = launch_pack(A, B, ab_dtype, A_pack, Bt_pack, K, N, r, io_dtype, stream);
+  if (!aligned16(pack)) { set_error("pack_lora: pack buffer must be 16-byte aligned"); return B200LORA_E_ALIGN; }
+  char* base = reinterpret_cast<char*>(pack);
+  void* A_pack = base;
+  void* Bt_pack = base + 2ll * 16 * K;
+  void* Bn_pack = base + 2ll * 16 * (K + N);
+  void* At_pack = base + 2ll * (16 * (K + N) + 64ll * N);
+  cudaError_t e = launch_pack(A, B, ab_dtype, bias, bias_dtype, A_pack, Bt_pack, Bn_pack, At_pack, K,
+                              N, r, io_dtype, stream);
   if (e != cudaSuccess) { set_error("pack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
@@ -247,12 +276,14 @@ extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, vo
 extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int64_t ldw,
                                   int w_layout, const void* bias, int bias_dtype, const void* S1,
                                   int64_t s1_rs, int64_t s1_cs, const void* S1_pack, const void* S2,
-                                  int64_t s2_rs, int64_t s2_cs, int ab_dtype, float scale, void* Y,
-                                  int64_t ldy, void* T_out, int64_t M, int Kc, int Nout, int r,
-                                  int io_dtype, int impl, b200lora_stream_t stream_) {
+                                  int64_t s2_rs, int64_t s2_cs, int ab_dtype, const void* S2_pack,
+                                  float scale, void* Y, int64_t ldy, void* T_out, int64_t M, int Kc,
+                                  int Nout, int r, int io_dtype, int impl,
+                                  b200lora_stream_t stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   g_err[0] = 0;
-  if (!X || !W || !S2 || !Y || (!S1 && !S1_pack)) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  const bool have_packs = S1_pack && S2_pack;
+  if (!X || !W || !Y || (!(S1 && S2) && !have_packs)) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (!valid_dtype(io_dtype) || !valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype))) {
     set_error("bad dtype enum"); return B200LORA_E_DTYPE;
   }
@@ -264,14 +295,14 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
   }
   if (impl == B200LORA_IMPL_TC || impl == B200LORA_IMPL_AUTO) {
     bool ok = tc_applicable(X, ldx, W, ldw, w_layout, Y, ldy, r, io_dtype, Nout);
-    if (ok && (!S1_pack || !aligned16(S1_pack) || (Kc % 8))) {
-      set_error("tc path needs the packed rank rows (b200lora_pack_lora) 16-byte aligned");
+    if (ok && (!have_packs || !aligned16(S1_pack) || !aligned16(S2_pack) || (Kc % 8))) {
+      set_error("tc path needs the packed LoRA operands (b200lora_pack_lora), 16-byte aligned");
       ok = false;
       if (impl == B200LORA_IMPL_TC) return B200LORA_E_ARG;
     }
     if (ok)
-      return run_tc(X, ldx, W, ldw, bias, bias_dtype, S1_pack, S2, s2_rs, s2_cs, ab_dtype, scale, Y,
-                    ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
+      return run_tc(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale, Y, ldy, T_out, M, Kc,
+                    Nout, r, io_dtype, stream);
     if (impl == B200LORA_IMPL_TC) {
       if (io_dtype == B200LORA_F32) return B200LORA_E_DTYPE;
       DevInfo di = dev_info();
@@ -280,30 +311,36 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
     }
     g_err[0] = 0;
   }
-  if (!S1) { set_error("simt path needs the unpacked rank rows S1"); return B200LORA_E_ARG; }
+  if (!S1 || !S2) { set_error("simt path needs the unpacked LoRA factors S1/S2"); return B200LORA_E_ARG; }
   return run_simt(X, ldx, W, ldw, w_layout, bias, bias_dtype, S1, s1_rs, s1_cs, S2, s2_rs, s2_cs,
                   ab_dtype, scale, Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
 }
 
 extern "C" int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
-                                   const void* A, const void* B, int ab_dtype, const void* A_pack,
+                                   const void* A, const void* B, int ab_dtype, const void* pack,
                                    float scale, void* Y, void* T_out, int64_t M, int K, int N,
                                    int r, int io_dtype, int impl, b200lora_stream_t stream) {
-  // S1 = A [r,K] (row stride K), S2 = B [N,r] (row stride r)
-  return b200lora_lora_gemm(X, K, W0, K, B200LORA_W_NK, bias, bias_dtype, A, K, 1, A_pack, B, r, 1,
-                            ab_dtype, scale, Y, N, T_out, M, K, N, r, io_dtype, impl, stream);
+  // S1 = A [r,K] (row stride K), S2 = B [N,r] (row stride r); packs: A_pack and Bn_pack
+  const char* pk = reinterpret_cast<const char*>(pack);
+  const void* s1p = pk;
+  const void* s2p = pk ? pk + 2ll * 16 * ((int64_t)K + N) : nullptr;
+  return b200lora_lora_gemm(X, K, W0, K, B200LORA_W_NK, bias, bias_dtype, A, K, 1, s1p, B, r, 1,
+                            ab_dtype, s2p, scale, Y, N, T_out, M, K, N, r, io_dtype, impl, stream);
 }
 
 extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout, const void* A,
-                                      const void* B, int ab_dtype, const void* Bt_pack, float scale,
+                                      const void* B, int ab_dtype, const void* pack, float scale,
                                       void* dX, void* dT_out, int64_t M, int K, int N, int r,
                                       int io_dtype, int impl, b200lora_stream_t stream) {
   // dX = dY·W0 + (s·dY·B)·A : contraction over N.  S1 = Bᵀ (logical [r,N]: (j,n) -> B[n*r+j]),
   // S2 = Aᵀ (logical [K,r]: (k,j) -> A[j*K+k]).  W as [K,N] (NK layout of the transposed
-  // problem) or W0 itself [N,K] (KN layout).
+  // problem) or W0 itself [N,K] (KN layout).  packs: Bt_pack and At_pack
   const int64_t ldw = (w_layout == B200LORA_W_NK) ? N : K;
-  return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, Bt_pack, A, 1, K,
-                            ab_dtype, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+  const char* pk = reinterpret_cast<const char*>(pack);
+  const void* s1p = pk ? pk + 2ll * 16 * K : nullptr;
+  const void* s2p = pk ? pk + 2ll * (16 * ((int64_t)K + N) + 64ll * N) : nullptr;
+  return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, s1p, A, 1, K, ab_dtype,
+                            s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
 }
 
 extern "C" int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r) {

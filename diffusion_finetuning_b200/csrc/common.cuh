@@ -41,14 +41,13 @@ struct TcParams {
   long long M;
   int Kc, Nout, r, BN;
   int num_m_blk, num_n_blk, num_k_blk, stages;
+  int nst, acc_stride;        // TMEM accumulator stages and their column stride
+  int has_bias, tail_ksteps;  // bias rides on a ones column of the tail MMA; K=16 steps in the tail
   float scale;
-  const void* S1; long long s1_rs, s1_cs;
-  const void* S2; long long s2_rs, s2_cs;
-  int ab_dtype;
-  const void* bias; int bias_dtype;
   void* T_out;
-  void* Y; long long ldy;
-  unsigned idesc_main, idesc_tail;
+  unsigned idesc_main, idesc_main_t, idesc_tail;
+  long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
+  int dbg_cta;
 };
 
 // ---- error plumbing (api.cu owns the storage) ----

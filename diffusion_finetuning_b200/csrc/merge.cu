@@ -155,37 +155,56 @@ cudaError_t launch_svd_epilogue(float* U, const float* S, float* Vh, float hi, i
   return cudaGetLastError();
 }
 
-// ---- LoRA pack: A -> A_pack [16,K], B -> Bt_pack [16,N] (= Bᵀ), both in the io dtype with rows
-// r..15 zero.  These are the TMA-loadable "rank rows" of the fused GEMM (forward uses A_pack,
-// backward-dX uses Bt_pack).  One launch per (A,B) version; O(16·(K+N)) elements.
+// ---- LoRA pack: the TMA-loadable operands of the fused tcgen05 GEMM, all in the io dtype ----
+//   A_pack  [16, K]  = A  rows (lora_down.weight), rows r..15 zero      forward  rank rows  (S1)
+//   Bt_pack [16, N]  = Bᵀ rows (lora_up.weight),   rows r..15 zero      backward rank rows  (S1)
+//   Bn_pack [N, 64]  = B  rows, column r = bias[n] (if any), rest zero  forward  tail block (S2)
+//   At_pack [K, 64]  = Aᵀ rows, columns r..63 zero                      backward tail block (S2)
+// One launch per (A, B) version; O(80·(K+N)) elements.
 template <typename TIO>
 __global__ void lora_pack_kernel(const void* __restrict__ A, const void* __restrict__ B, int ab_dtype,
-                                 TIO* __restrict__ A_pack, TIO* __restrict__ Bt_pack, int K, int N,
+                                 const void* __restrict__ bias, int bias_dtype,
+                                 TIO* __restrict__ A_pack, TIO* __restrict__ Bt_pack,
+                                 TIO* __restrict__ Bn_pack, TIO* __restrict__ At_pack, int K, int N,
                                  int r) {
-  const int total = 16 * (K + N);
+  const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    if (i < 16 * K) {
+    if (i < n0) {
       const int j = i / K, k = i - j * K;
       A_pack[i] = from_f32<TIO>(j < r ? load_as_float(A, ab_dtype, (long long)j * K + k) : 0.f);
-    } else {
-      const int t = i - 16 * K;
+    } else if (i < n1) {
+      const int t = i - n0;
       const int j = t / N, n = t - j * N;
       Bt_pack[t] = from_f32<TIO>(j < r ? load_as_float(B, ab_dtype, (long long)n * r + j) : 0.f);
+    } else if (i < n2) {
+      const int t = i - n1;
+      const int n = t >> 6, j = t & 63;
+      float v = 0.f;
+      if (j < r) v = load_as_float(B, ab_dtype, (long long)n * r + j);
+      else if (j == r && bias != nullptr) v = load_as_float(bias, bias_dtype, n);
+      Bn_pack[t] = from_f32<TIO>(v);
+    } else {
+      const int t = i - n2;
+      const int k = t >> 6, j = t & 63;
+      At_pack[t] = from_f32<TIO>(j < r ? load_as_float(A, ab_dtype, (long long)j * K + k) : 0.f);
     }
   }
 }
 
-cudaError_t launch_pack(const void* A, const void* B, int ab_dtype, void* A_pack, void* Bt_pack,
-                        int K, int N, int r, int io_dtype, cudaStream_t stream) {
-  const int total = 16 * (K + N);
+cudaError_t launch_pack(const void* A, const void* B, int ab_dtype, const void* bias, int bias_dtype,
+                        void* A_pack, void* Bt_pack, void* Bn_pack, void* At_pack, int K, int N,
+                        int r, int io_dtype, cudaStream_t stream) {
+  const int total = 80 * (K + N);
   int blocks = (total + 255) / 256;
-  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks > 148 * 8) blocks = 148 * 8;
   if (io_dtype == B200LORA_BF16)
     lora_pack_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
-        A, B, ab_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack, K, N, r);
+        A, B, ab_dtype, bias, bias_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack,
+        (__nv_bfloat16*)Bn_pack, (__nv_bfloat16*)At_pack, K, N, r);
   else
-    lora_pack_kernel<__half><<<blocks, 256, 0, stream>>>(A, B, ab_dtype, (__half*)A_pack,
-                                                         (__half*)Bt_pack, K, N, r);
+    lora_pack_kernel<__half><<<blocks, 256, 0, stream>>>(
+        A, B, ab_dtype, bias, bias_dtype, (__half*)A_pack, (__half*)Bt_pack, (__half*)Bn_pack,
+        (__half*)At_pack, K, N, r);
   return cudaGetLastError();
 }
 

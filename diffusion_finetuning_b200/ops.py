@@ -53,26 +53,29 @@ class BaseWeightCache:
         self._store[slot] = (key, out)
         return out
 
-    def lora_pack(self, A, B, dtype):
-        """(A_pack [16,K], Bt_pack [16,N]) in `dtype`: the TMA-loadable rank rows of the tcgen05
-        kernel (b200lora_pack_lora).  Re-packed (one tiny launch, fresh buffer) whenever either
-        factor changes: optimizer steps bump `_version`, monkeypatch_* swap the Parameter."""
-        key = (self._key(A), self._key(B), dtype)
+    def lora_pack(self, A, B, bias, dtype):
+        """The packed LoRA operands of the tcgen05 kernel (b200lora_pack_lora): one buffer of
+        80·(K+N) elements in `dtype` holding the rank rows and tail blocks of forward and backward
+        (and the frozen bias, which the forward adds through the tail MMA).  Re-packed (one tiny
+        launch, fresh buffer) whenever either factor changes: optimizer steps bump `_version`,
+        monkeypatch_* swap the Parameter."""
+        key = (self._key(A), self._key(B), None if bias is None else self._key(bias), dtype)
         hit = self._store.get("pack")
         if hit is not None and hit[0] == key:
             return hit[1]
         r, K = A.shape
         N = B.shape[0]
-        buf = torch.empty(16 * (K + N), dtype=dtype, device=A.device)
-        a_pack, bt_pack = buf[:16 * K].view(16, K), buf[16 * K:].view(16, N)
+        buf = torch.empty(80 * (K + N), dtype=dtype, device=A.device)
         Ac, Bc = A.detach().contiguous(), B.detach().contiguous()
+        bc = None if bias is None else bias.detach().contiguous()
         with torch.cuda.device(A.device):
             rc = nat.lib().b200lora_pack_lora(nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype),
-                                              nat.ptr(a_pack), nat.ptr(bt_pack), K, N, r,
-                                              nat.dtype_code(dtype), nat.stream_ptr(A.device))
+                                              nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
+                                              nat.ptr(buf), K, N, r, nat.dtype_code(dtype),
+                                              nat.stream_ptr(A.device))
         nat.check(rc, "b200lora_pack_lora")
-        self._store["pack"] = (key, (a_pack, bt_pack))
-        return a_pack, bt_pack
+        self._store["pack"] = (key, buf)
+        return buf
 
     def invalidate(self):
         self._store.clear()
@@ -181,28 +184,28 @@ class _LoraLinearFn(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
         y = torch.empty((M, N), dtype=cdt, device=x.device)
         T = torch.empty((M, r), dtype=cdt, device=x.device) if need_grad else None
-        a_pack = bt_pack = None
+        pack = None
         if use_tc and M > 0:
-            a_pack, bt_pack = cache.lora_pack(A, B, cdt)
+            pack = cache.lora_pack(A, B, bias, cdt)
         if M > 0:
             with torch.cuda.device(x.device), _Prof("fwd", M, K, N, r, x2.element_size()):
                 rc = lib.b200lora_linear_fwd(
                     nat.ptr(x2), nat.ptr(w), nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
-                    nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype), nat.ptr(a_pack), float(scale),
+                    nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype), nat.ptr(pack), float(scale),
                     nat.ptr(y), nat.ptr(T), M, K, N, r, nat.dtype_code(cdt),
                     nat.IMPL_TC if use_tc else nat.IMPL_SIMT, nat.stream_ptr(x.device))
                 nat.check(rc, "b200lora_linear_fwd")
         if need_grad:
             ctx.save_for_backward(x2, T, A, B, w0, w)
             ctx.meta = (lead, M, K, N, r, float(scale), cdt, use_tc, cache, bool(deterministic),
-                        x.dtype, bias is not None, bt_pack, sink)
+                        x.dtype, bias is not None, pack, sink)
         return y.reshape(*lead, N)
 
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, dy):
         x2, T, A, B, w0, w = ctx.saved_tensors
-        (lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias, bt_pack,
+        (lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias, pack,
          sink) = ctx.meta
         lib = nat.lib()
         dev = dy.device
@@ -231,7 +234,7 @@ class _LoraLinearFn(torch.autograd.Function):
                 prof.__enter__()
                 if use_tc:
                     rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(wt), nat.W_NK, nat.ptr(Ac),
-                                                    nat.ptr(Bc), ab_code, nat.ptr(bt_pack), scale, nat.ptr(dx),
+                                                    nat.ptr(Bc), ab_code, nat.ptr(pack), scale, nat.ptr(dx),
                                                     nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_TC, stream)
                 else:
                     rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(w), nat.W_KN, nat.ptr(Ac),

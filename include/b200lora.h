@@ -72,12 +72,13 @@ int b200lora_tc_supported(void);
  * S1[j*s1_rs + k*s1_cs], S2 logical [Nout,r] with element (n,j) at S2[n*s2_rs + j*s2_cs].
  * io_dtype is the type of X, W, Y and T_out; ab_dtype the type of S1/S2 (fp32 masters
  * under autocast are read directly); bias may be NULL.
- * The tcgen05 path fetches the rank rows by TMA from S1_pack (see b200lora_pack_lora) and
- * ignores S1; the SIMT path reads S1 with its strides and ignores S1_pack.  Either may be NULL
- * if the selected path does not need it.
- * On the tcgen05 path this is ONE kernel: the rank-r rows ride along as 16 extra
- * accumulator columns of the same MMA and the up-projection is one more K=16 MMA step
- * ([X | sT]·[Wᵀ ; S2ᵀ]), so no separate low-rank GEMM or elementwise add runs.
+ * The tcgen05 path fetches the rank rows and the tail block by TMA from S1_pack / S2_pack (see
+ * b200lora_pack_lora) and ignores S1/S2; the bias it adds is the one PACKED into S2_pack (`bias`
+ * only says whether there is one).  The SIMT path reads S1/S2/bias with their strides and ignores
+ * the packs.  Either set may be NULL if the selected path does not need it.
+ * On the tcgen05 path this is ONE kernel: the rank rows ride along as 16 extra accumulator
+ * columns of the same MMA and the up-projection AND the bias are one more K=16 MMA step
+ * ([X | sT | 1]·[Wᵀ ; S2ᵀ ; bias]), so no separate low-rank GEMM or elementwise add runs.
  */
 int b200lora_lora_gemm(const void* X, int64_t ldx,
                        const void* W, int64_t ldw, int w_layout,
@@ -85,6 +86,7 @@ int b200lora_lora_gemm(const void* X, int64_t ldx,
                        const void* S1, int64_t s1_rs, int64_t s1_cs,
                        const void* S1_pack /* [16,Kc] io dtype, rows >= r zero; tcgen05 path */,
                        const void* S2, int64_t s2_rs, int64_t s2_cs, int ab_dtype,
+                       const void* S2_pack /* [Nout,64] io dtype: S2 | bias | 0; tcgen05 path */,
                        float scale,
                        void* Y, int64_t ldy,
                        void* T_out /* nullable, [M,r] compact */,
@@ -92,13 +94,18 @@ int b200lora_lora_gemm(const void* X, int64_t ldx,
                        int io_dtype, int impl, b200lora_stream_t stream);
 
 /*
- * Pack the LoRA factors for the tcgen05 path (one tiny launch per weight version):
- *   A_pack  [16,K] = A  (lora_down.weight [r,K]) zero-padded to 16 rows, in io_dtype
- *   Bt_pack [16,N] = Bᵀ (lora_up.weight   [N,r]) zero-padded to 16 rows, in io_dtype
- * These are the TMA-loadable rank rows that ride along as 16 extra MMA columns; fp32 masters
- * (autocast) are rounded to io_dtype here, as autocast would round them.
+ * Pack the LoRA factors for the tcgen05 path (one tiny launch per weight version) into ONE
+ * buffer of b200lora_pack_elems(K, N) = 80·(K+N) elements of io_dtype, laid out as
+ *   A_pack  [16,K] @ 0                 A  rows zero-padded to 16 (forward rank rows)
+ *   Bt_pack [16,N] @ 16·K              Bᵀ rows zero-padded to 16 (backward rank rows)
+ *   Bn_pack [N,64] @ 16·(K+N)          B rows | bias[n] in column r | zeros (forward tail block)
+ *   At_pack [K,64] @ 16·(K+N) + 64·N   Aᵀ rows | zeros                     (backward tail block)
+ * fp32 masters (autocast) are rounded to io_dtype here, as autocast would round them; `bias`
+ * (nullable) is the frozen bias of the base layer (lora.py:34), added by the forward tail MMA.
  */
-int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, void* A_pack, void* Bt_pack,
+int64_t b200lora_pack_elems(int K, int N);
+int b200lora_pack_lora(const void* A, const void* B, int ab_dtype,
+                       const void* bias, int bias_dtype, void* pack,
                        int K, int N, int r, int io_dtype, b200lora_stream_t stream);
 
 /*
@@ -109,7 +116,7 @@ int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, void* A_pack,
  */
 int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bias_dtype,
                         const void* A, const void* B, int ab_dtype,
-                        const void* A_pack /* from b200lora_pack_lora; NULL on the SIMT path */,
+                        const void* pack /* from b200lora_pack_lora; NULL on the SIMT path */,
                         float scale,
                         void* Y, void* T_out,
                         int64_t M, int K, int N, int r,
@@ -124,7 +131,7 @@ int b200lora_linear_fwd(const void* X, const void* W0, const void* bias, int bia
  */
 int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout,
                            const void* A, const void* B, int ab_dtype,
-                           const void* Bt_pack /* from b200lora_pack_lora; NULL on the SIMT path */,
+                           const void* pack /* from b200lora_pack_lora; NULL on the SIMT path */,
                            float scale,
                            void* dX, void* dT_out,
                            int64_t M, int K, int N, int r,

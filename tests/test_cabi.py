@@ -29,14 +29,15 @@ def test_library_builds_and_exports_header_symbols():
 
 def test_argument_validation_needs_no_gpu():
     lib = nat.lib()
-    rc = lib.b200lora_lora_gemm(None, 0, None, 0, 0, None, 0, None, 0, 0, None, None, 0, 0, 0, 1.0, None, 0,
+    rc = lib.b200lora_lora_gemm(None, 0, None, 0, 0, None, 0, None, 0, 0, None, None, 0, 0, 0, None, 1.0, None, 0,
                                 None, 4, 8, 8, 2, nat.BF16, nat.IMPL_AUTO, None)
     assert rc == -6 and b"null" in lib.b200lora_last_error()
     buf = ctypes.create_string_buffer(64)
     p = ctypes.cast(buf, ctypes.c_void_p)
-    rc = lib.b200lora_lora_gemm(p, 8, p, 8, 0, None, 0, p, 8, 1, None, p, 2, 1, 7, 1.0, p, 8, None, 4, 8, 8, 2,
+    rc = lib.b200lora_lora_gemm(p, 8, p, 8, 0, None, 0, p, 8, 1, None, p, 2, 1, 7, None, 1.0, p, 8, None, 4, 8, 8, 2,
                                 nat.BF16, nat.IMPL_AUTO, None)
     assert rc == -4                                   # bad dtype enum
     rc = lib.b200lora_merge(p, p, p, p, 1.0, 4, 6, 2, nat.BF16, nat.BF16, None)
     assert rc == -3                                   # K % 8 != 0 for 16-bit weights
     assert lib.b200lora_lora_grads_workspace(4096, 320, 320, 4) > 0
+    assert lib.b200lora_pack_elems(320, 640) == 80 * 960

@@ -43,14 +43,14 @@ def run_cabi(dev, M, K, N, r, s, dtype, impl):
     y = torch.empty(M, N, dtype=dtype, device=DEV)
     T = torch.empty(M, r, dtype=dtype, device=DEV)
     b = dev["b"]
-    a_pack = bt_pack = None
+    pack = None
     if impl == nat.IMPL_TC:
-        a_pack = torch.empty(16, K, dtype=dtype, device=DEV)
-        bt_pack = torch.empty(16, N, dtype=dtype, device=DEV)
-        nat.check(lib.b200lora_pack_lora(nat.ptr(dev["A"]), nat.ptr(dev["B"]), ab, nat.ptr(a_pack),
-                                         nat.ptr(bt_pack), K, N, r, io, st), "pack")
+        assert lib.b200lora_pack_elems(K, N) == 80 * (K + N)
+        pack = torch.empty(80 * (K + N), dtype=dtype, device=DEV)
+        nat.check(lib.b200lora_pack_lora(nat.ptr(dev["A"]), nat.ptr(dev["B"]), ab, nat.ptr(b), io, nat.ptr(pack),
+                                         K, N, r, io, st), "pack")
     nat.check(lib.b200lora_linear_fwd(nat.ptr(dev["x"]), nat.ptr(dev["w0"]), nat.ptr(b), io, nat.ptr(dev["A"]),
-                                      nat.ptr(dev["B"]), ab, nat.ptr(a_pack), s, nat.ptr(y), nat.ptr(T), M, K, N, r,
+                                      nat.ptr(dev["B"]), ab, nat.ptr(pack), s, nat.ptr(y), nat.ptr(T), M, K, N, r,
                                       io, impl, st), "fwd")
     dx = torch.empty(M, K, dtype=dtype, device=DEV)
     dT = torch.empty(M, r, dtype=dtype, device=DEV)
@@ -60,7 +60,7 @@ def run_cabi(dev, M, K, N, r, s, dtype, impl):
     else:
         w, lay = dev["w0"], nat.W_KN
     nat.check(lib.b200lora_linear_bwd_dx(nat.ptr(dev["dy"]), nat.ptr(w), lay, nat.ptr(dev["A"]), nat.ptr(dev["B"]),
-                                         ab, nat.ptr(bt_pack), s, nat.ptr(dx), nat.ptr(dT), M, K, N, r, io, impl, st),
+                                         ab, nat.ptr(pack), s, nat.ptr(dx), nat.ptr(dT), M, K, N, r, io, impl, st),
               "bwd_dx")
     dA = torch.zeros(r, K, dtype=torch.float32, device=DEV)
     dB = torch.zeros(N, r, dtype=torch.float32, device=DEV)

@@ -51,6 +51,9 @@ def main():
     ap.add_argument("--r", type=int, default=4)
     ap.add_argument("--json", default=None)
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--shapes", default=None, help="comma list of indices into CENSUS")
+    ap.add_argument("--back2back", type=int, default=0,
+                    help="also time N back-to-back launches (no L2 flush, launch latency overlapped)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     lib = nat.lib()
@@ -60,7 +63,8 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
     r = args.r
     rows = []
-    for (M, K, N, count) in CENSUS:
+    census = CENSUS if args.shapes is None else [CENSUS[int(i)] for i in args.shapes.split(",")]
+    for (M, K, N, count) in census:
         x = torch.randn(M, K, device=dev, dtype=dt)
         w = (torch.rand(N, K, device=dev) * 2 - 1).mul_(K ** -0.5).to(dt)
         wt = w.t().contiguous()
@@ -75,9 +79,8 @@ def main():
         dA = torch.zeros(r, K, device=dev)
         dB = torch.zeros(N, r, device=dev)
 
-        a_pack = torch.empty(16, K, dtype=dt, device=dev)
-        bt_pack = torch.empty(16, N, dtype=dt, device=dev)
-        nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), io, nat.ptr(a_pack), nat.ptr(bt_pack), K, N, r, io,
+        a_pack = bt_pack = torch.empty(80 * (K + N), dtype=dt, device=dev)
+        nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), io, nat.ptr(b), io, nat.ptr(a_pack), K, N, r, io,
                                          st), "pack")
 
         def fwd():
@@ -104,6 +107,18 @@ def main():
                "grads_us": t_g * 1e6, "fwd_tflops": (2.0 * M * K * N + 2.0 * M * r * (K + N)) / t_f / 1e12,
                "fwdbwd_tflops": flops / (t_f + t_b + t_g) / 1e12, "ceiling_tflops": ceil_tf,
                "grads_gbs": e * (M * K + M * N + 2 * M * r) / t_g / 1e9}
+        if args.back2back:
+            def b2b(fn):
+                fn(); torch.cuda.synchronize()
+                a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda._sleep(2000000)
+                a.record()
+                for _ in range(args.back2back):
+                    fn()
+                b_.record()
+                torch.cuda.synchronize()
+                return a.elapsed_time(b_) * 1e3 / args.back2back
+            row.update({"fwd_b2b_us": b2b(fwd), "bwd_dx_b2b_us": b2b(bdx), "grads_b2b_us": b2b(grads)})
         if not args.no_torch:
             xr = x.clone().requires_grad_(True)
             Ar, Br = A.clone().requires_grad_(True), B.clone().requires_grad_(True)

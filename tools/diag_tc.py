@@ -51,9 +51,8 @@ def run_case(idx):
     y = torch.full((M, N), float("nan"), dtype=dtype, device=dev)
     T = torch.full((M, r), float("nan"), dtype=dtype, device=dev)
     io = nat.dtype_code(dtype)
-    a_pack = torch.empty(16, K, dtype=dtype, device=dev)
-    bt_pack = torch.empty(16, N, dtype=dtype, device=dev)
-    nat.check(lib.b200lora_pack_lora(nat.ptr(Ad), nat.ptr(Bd), io, nat.ptr(a_pack), nat.ptr(bt_pack), K, N, r, io,
+    a_pack = torch.empty(80 * (K + N), dtype=dtype, device=dev)
+    nat.check(lib.b200lora_pack_lora(nat.ptr(Ad), nat.ptr(Bd), io, nat.ptr(bd), io, nat.ptr(a_pack), K, N, r, io,
                                      nat.stream_ptr(dev)), "pack")
     rc = lib.b200lora_linear_fwd(nat.ptr(xd), nat.ptr(wd), nat.ptr(bd), io, nat.ptr(Ad), nat.ptr(Bd), io,
                                  nat.ptr(a_pack), s, nat.ptr(y), nat.ptr(T), M, K, N, r, io, nat.IMPL_TC,

@@ -37,9 +37,8 @@ def main():
     dT = torch.empty(M, r, device=dev, dtype=dt)
     dA = torch.zeros(r, K, device=dev)
     dB = torch.zeros(N, r, device=dev)
-    ap_ = torch.empty(16, K, dtype=dt, device=dev)
-    bp_ = torch.empty(16, N, dtype=dt, device=dev)
-    nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), io, nat.ptr(ap_), nat.ptr(bp_), K, N, r, io, st), "pack")
+    ap_ = bp_ = torch.empty(80 * (K + N), dtype=dt, device=dev)
+    nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), io, nat.ptr(b), io, nat.ptr(ap_), K, N, r, io, st), "pack")
     w32 = torch.randn(N, K, device=dev)
     for _ in range(a.reps):
         if a.what in ("fwd", "all"):
