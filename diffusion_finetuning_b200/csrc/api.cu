@@ -29,6 +29,10 @@ unsigned int tc_read_watchdog();
 template <typename TIO>
 cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                       const CUtensorMap&, const TcParams&, int, int, cudaStream_t);
+int tc2_smem_bytes(int BN, int* stages_out);
+template <typename TIO>
+cudaError_t launch_tc2(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                       const CUtensorMap&, const CUtensorMap&, const TcParams&, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
                         int, int, int, int, cudaStream_t);
 template <typename TIO>
@@ -206,6 +210,68 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
   return 0;
 }
 
+// CTA-pair variant (linear_tc2.cu): same math, tcgen05 cta_group::2, 256-row blocks per pair
+static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, bool has_bias,
+                   const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
+                   void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
+                   cudaStream_t stream) {
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
+  p.BN = tc_pick_bn(Nout);
+  p.num_m_blk = (int)((M + 255) / 256);
+  p.num_n_blk = (Nout + p.BN - 1) / p.BN;
+  p.num_k_blk = (Kc + 63) / 64;
+  const int smem = tc2_smem_bytes(p.BN, &p.stages);
+  if (p.stages < 2) { set_error("tc2: not enough shared memory for BN=%d", p.BN); return B200LORA_E_SHAPE; }
+  tc_tmem_plan(p.BN, &p.nst, &p.acc_stride);
+  p.scale = scale;
+  p.has_bias = has_bias ? 1 : 0;
+  p.tail_ksteps = (r + p.has_bias > 16) ? 2 : 1;
+  p.T_out = T_out;
+  p.dbg = g_dbg_buf;
+  p.dbg_cta = g_dbg_cta;
+  const unsigned fmt = io_dtype == B200LORA_BF16 ? 1u : 0u;
+  const unsigned base = (1u << 4) | (fmt << 7) | (fmt << 10) | ((256u >> 4) << 24);   // M = 256
+  p.idesc_main = base | (((unsigned)p.BN >> 3) << 17);
+  p.idesc_main_t = base | (((unsigned)(p.BN + 16) >> 3) << 17);
+  p.idesc_tail = p.idesc_main;
+  const int H = (p.BN + 16) / 2;
+
+  CUtensorMap tmX, tmWa, tmWb, tmS1, tmS2, tmY;
+  int rc;
+  if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmWa, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)(H - 16), 64,
+                     io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmWb, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)H, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;   // leader: H rows in one box
+  if ((rc = get_tmap(&tmS1, S1_pack, 16, (uint64_t)Kc, (uint64_t)Kc, 16, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmS2, S2_pack, (uint64_t)Nout, 64, 64, (uint32_t)(p.BN / 2), 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  cudaError_t e = io_dtype == B200LORA_BF16
+                      ? launch_tc2<__nv_bfloat16>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream)
+                      : launch_tc2<__half>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream);
+  if (e != cudaSuccess) {
+    set_error("tc2 launch failed: %s", cudaGetErrorString(e));
+    return B200LORA_E_CUDA;
+  }
+  return 0;
+}
+
+// B200LORA_PAIR=0 selects the single-CTA kernel (linear_tc.cu), anything else the CTA-pair kernel
+static bool use_pair() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200LORA_PAIR");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 static int run_simt(const void* X, long long ldx, const void* W, long long ldw, int w_layout,
                     const void* bias, int bias_dtype, const void* S1, long long s1_rs,
                     long long s1_cs, const void* S2, long long s2_rs, long long s2_cs, int ab_dtype,
@@ -301,8 +367,8 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
       if (impl == B200LORA_IMPL_TC) return B200LORA_E_ARG;
     }
     if (ok)
-      return run_tc(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale, Y, ldy, T_out, M, Kc,
-                    Nout, r, io_dtype, stream);
+      return (use_pair() ? run_tc2 : run_tc)(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale,
+                                             Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
     if (impl == B200LORA_IMPL_TC) {
       if (io_dtype == B200LORA_F32) return B200LORA_E_DTYPE;
       DevInfo di = dev_info();

@@ -1,0 +1,533 @@
+// Fused LoRA GEMM for sm_100a, CTA-PAIR version: tcgen05.mma.cta_group::2 (UMMA M = 256 over two
+// SMs of one TPC), TMA -> smem (128B swizzle) -> TMEM -> TMA store.
+//
+//   T = X · S1ᵀ                       [M, r]
+//   Y = X · Wᵀ + bias + (s·T) · S2ᵀ   [M, Nout]        ( = [X | sT | 1] · [Wᵀ ; S2ᵀ ; bias] )
+//
+// Why a pair: the single-CTA kernel (linear_tc.cu) moves (128 + BN + 16)·128 B from L2 per k-block
+// per 128 x BN tile and was measured AT the L2->SM throughput cap (~12 TB/s) on every large shape.
+// In a pair each CTA loads its own 128 rows of X but only HALF of the W tile; the MMA reads the
+// two halves from both CTAs' shared memory.  Per CTA and k-block: 16 KB + (BN+16)/2·128 B, i.e.
+// ~30 % less L2 traffic at BN = 160, and half the smem footprint for W (6 pipeline stages).
+//
+// Per CTA (512 threads), roles as in linear_tc.cu:
+//   warp 0       TMA producer (BOTH CTAs): own X rows + own half of [W rows ; 16 rank rows]; all
+//                transaction bytes of a stage are signalled on the LEADER's full barrier
+//   warp 1       MMA issuer (leader CTA only, one thread): main loop N = BN+16 (the rank rows ride
+//                along as 16 extra accumulator columns = T), tail K=16 step(s) [sT | 1]·[S2 | bias]ᵀ;
+//                tcgen05.commit multicasts to the barriers of both CTAs
+//   warp 2       TMEM allocator (cta_group::2, both CTAs)
+//   warps 4-7    T step for the CTA's own 128 rows (first tile of a row block only); arrives on
+//                the leader's barrier through shared::cluster
+//   warps 8-15   epilogue for the CTA's own 128 rows: pipelined tcgen05.ld -> staging -> TMA store
+// A pair owns a contiguous range of (256-row block, n-tile) pairs in n-fastest order.
+#include <cooperative_groups.h>
+
+#include "ptx.cuh"
+#include "common.cuh"
+
+namespace b200 {
+
+namespace tc2 {
+constexpr int BM = 128;          // rows per CTA == TMEM lanes
+constexpr int BK = 64;
+constexpr int RP = 16;
+constexpr int UK = 16;
+constexpr int EPI_COLS = 32;
+constexpr int MAX_STAGES = 8;
+constexpr int MAX_ACC = 4;
+constexpr int MAX_CI = 4;
+constexpr int NUM_THREADS = 512;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int A_TILE_BYTES = BM * 128;
+constexpr int T_TILE_BYTES = BM * 128;
+constexpr int STAGING_BYTES = NUM_EPI_WARPS * 2 * 32 * EPI_COLS * 2;
+constexpr int BAR_BYTES = 1024;
+
+__host__ __device__ inline int half_rows(int BN) { return (BN + RP) / 2; }   // B rows per CTA
+__host__ __device__ inline int stage_bytes(int BN) { return A_TILE_BYTES + half_rows(BN) * 128; }
+__host__ __device__ inline int fixed_bytes() { return T_TILE_BYTES + STAGING_BYTES + BAR_BYTES; }
+}  // namespace tc2
+
+template <typename TIO>
+__device__ __forceinline__ uint32_t pack2b(float a, float b);
+template <>
+__device__ __forceinline__ uint32_t pack2b<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2b<__half>(float a, float b) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+enum : uint32_t {
+  S2_PROD_EMPTY = 17, S2_MMA_ACC_EMPTY, S2_MMA_FULL, S2_MMA_TAIL_FULL, S2_MMA_TSM, S2_T_TFULL,
+  S2_T_FREE, S2_EPI_ACC
+};
+
+struct Sched2 {
+  int t0, t1, nnb;
+  __device__ __forceinline__ bool new_m(int tile) const { return tile == t0 || (tile % nnb) == 0; }
+  __device__ __forceinline__ bool look(int tile) const {
+    return new_m(tile) && tile + 1 < t1 && ((tile + 1) % nnb) != 0;
+  }
+};
+
+#define TS2(role, it_, k)                                                             \
+  do {                                                                                \
+    if (DBG && (int)blockIdx.x == p.dbg_cta && (it_) < 32)                            \
+      p.dbg[(role) * 256 + (it_) * 8 + (k)] = clock64();                              \
+  } while (0)
+
+template <typename TIO, bool DBG>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc2::NUM_THREADS, 1)
+lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmWa,
+                     const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmS1,
+                     const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmY,
+                     const TcParams p) {
+  using namespace tc2;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int BN = p.BN;
+  const int H = half_rows(BN);
+  const int stages = p.stages;
+  const int stg_bytes = stage_bytes(BN);
+  uint8_t* stage_base = smem;
+  uint8_t* t_tile = stage_base + (size_t)stages * stg_bytes;
+  uint8_t* staging = t_tile + T_TILE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + STAGING_BYTES);
+  uint64_t* full_bar = bars;                      // [MAX_STAGES] leader's is the live one
+  uint64_t* empty_bar = bars + MAX_STAGES;        // [MAX_STAGES] per CTA (multicast commit)
+  uint64_t* accfull_bar = bars + 2 * MAX_STAGES;  // [MAX_ACC]    per CTA (multicast commit)
+  uint64_t* accempty_bar = accfull_bar + MAX_ACC; // [MAX_ACC]    leader's: 16 warp arrivals
+  uint64_t* tfull_bar = accempty_bar + MAX_ACC;   // [1] per CTA (multicast commit)
+  uint64_t* tsm_full_bar = tfull_bar + 1;         // [1] leader's: 256 thread arrivals
+  uint64_t* st_free_bar = tsm_full_bar + 1;       // [1] per CTA (multicast commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_free_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int num_tiles = p.num_m_blk * p.num_n_blk;     // num_m_blk counts 256-row blocks here
+  const int ncl = gridDim.x >> 1;
+  const int cl = blockIdx.x >> 1;
+  Sched2 sc;
+  sc.t0 = (int)((long long)cl * num_tiles / ncl);
+  sc.t1 = (int)((long long)(cl + 1) * num_tiles / ncl);
+  sc.nnb = p.num_n_blk;
+  const int NST = p.nst;
+  const int ACC_STRIDE = p.acc_stride;
+  if (threadIdx.x == 0) TS2(0, 0, 0);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmWa);
+    tma_prefetch_desc(&tmWh);
+    tma_prefetch_desc(&tmS1);
+    tma_prefetch_desc(&tmS2);
+    tma_prefetch_desc(&tmY);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 2);   // leader: arrive.expect_tx; peer: remote arrive
+      mbar_init(&empty_bar[s], 1);  // tcgen05.commit (multicast)
+    }
+    for (int a = 0; a < MAX_ACC; ++a) {
+      mbar_init(&accfull_bar[a], 1);
+      mbar_init(&accempty_bar[a], 2 * NUM_EPI_WARPS);
+    }
+    mbar_init(tfull_bar, 1);
+    mbar_init(tsm_full_bar, 256);
+    mbar_init(st_free_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_2sm(tmem_slot, 512);
+  }
+  tc_fence_before_sync();
+  cluster_sync_all();       // peer barriers initialised before any remote arrive / multicast commit
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) TS2(0, 0, 1);
+
+  if (warp == 0 || warp == 3) {
+    // =============================== TMA producers (both CTAs) ========================
+    // TMA issue is serial per thread (~130 cycles per cp.async.bulk.tensor): the loads of a stage
+    // are split over two threads.  warp 0 : the CTA's X rows + the arrive / expect_tx of the stage;
+    // warp 3 : the CTA's half of [W rows ; rank rows] and the tail blocks.
+    {
+      // the whole warp walks the schedule (warp-uniform control flow); one elected lane issues.
+      // With `if (lane == 0)` around the loop ptxas wraps every uniform-datapath instruction
+      // (UTMALDG / UTCHMMA / UTCBAR) in an ELECT + BRA.U.ANY convergence loop.
+      const bool xrole = warp == 0;
+      const uint64_t pol_x = policy_evict_normal();
+      const uint64_t pol_w = policy_evict_last();
+      int s = 0;
+      uint32_t ph = 0;
+      const uint32_t main_tx = 2u * (A_TILE_BYTES + H * 128);   // both CTAs' bytes of one stage
+      const uint32_t tail_tx = 2u * (BN / 2) * 128;
+      const uint32_t full0_base = mapa_shared(smem_u32(&full_bar[0]), 0);   // leader's full_bar[0]
+      auto load_main = [&](int n_blk, int m_blk) {
+        const int n0 = n_blk * BN;
+        for (int kb = 0; kb < p.num_k_blk; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);
+          uint8_t* a_dst = stage_base + (size_t)s * stg_bytes;
+          uint8_t* b_dst = a_dst + A_TILE_BYTES;
+          const uint32_t full0 = full0_base + s * 8;
+          if (elect_one()) {
+            if (xrole) {
+              if (leader) mbar_arrive_expect_tx(&full_bar[s], main_tx);
+              else mbar_arrive_cluster(full0);
+              tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
+            } else if (leader) {
+              // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
+              tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);                  // H rows
+            } else {
+              tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, n0 + H, pol_w);              // H-16 rows
+              tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
+            }
+          }
+          __syncwarp();
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      };
+      auto load_tail = [&](int n_blk) {
+        mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);
+        uint8_t* b_dst = stage_base + (size_t)s * stg_bytes + A_TILE_BYTES;
+        const uint32_t full0 = full0_base + s * 8;
+        if (elect_one()) {
+          if (xrole) {
+            if (leader) mbar_arrive_expect_tx(&full_bar[s], tail_tx);
+            else mbar_arrive_cluster(full0);
+          } else {
+            tma_load_2d_2sm(b_dst, &tmS2, full0, 0, n_blk * BN + (int)rank * (BN / 2), pol_w);
+          }
+        }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+      };
+      int pit = 0;
+      int n_blk = sc.t0 % p.num_n_blk, m_blk = sc.t0 / p.num_n_blk;
+      for (int tile = sc.t0; tile < sc.t1;) {
+        const bool lk = sc.look(tile);
+        int n1 = n_blk + 1, m1 = m_blk;
+        if (n1 == p.num_n_blk) { n1 = 0; ++m1; }
+        if (xrole && lane == 0) TS2(1, pit, 0);
+        load_main(n_blk, m_blk);
+        if (xrole && lane == 0) TS2(1, pit, 1);
+        if (lk) load_main(n1, m1);
+        load_tail(n_blk);
+        if (lk) load_tail(n1);
+        if (xrole && lane == 0) TS2(1, pit, 2);
+        if (lk) {
+          n_blk = n1 + 1; m_blk = m1;
+          if (n_blk == p.num_n_blk) { n_blk = 0; ++m_blk; }
+        } else {
+          n_blk = n1; m_blk = m1;
+        }
+        tile += lk ? 2 : 1;
+        pit += lk ? 2 : 1;
+      }
+    }
+  } else if (warp == 1) {
+    // =============================== MMA issuer (leader only) =========================
+    if (leader) {       // whole warp, warp-uniform; the elected lane issues MMAs and commits
+      int s = 0;
+      uint32_t ph = 0;
+      const uint64_t t_desc = make_desc_sw128(smem_u32(t_tile));
+      long long wsum = 0;   // DBG: cycles the issuer spent waiting for operands
+      auto main_loop = [&](int st) {
+        const uint32_t d_tmem = tmem_base + st * ACC_STRIDE;
+        for (int kb = 0; kb < p.num_k_blk; ++kb) {
+          long long w0 = 0;
+          if (DBG) w0 = clock64();
+          mbar_wait(&full_bar[s], ph, S2_MMA_FULL);
+          if (DBG) wsum += clock64() - w0;
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(stage_base + (size_t)s * stg_bytes);
+          const uint64_t a_desc = make_desc_sw128(a_addr);
+          const uint64_t b_desc = make_desc_sw128(a_addr + A_TILE_BYTES);
+          if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < BK / UK; ++k)
+              umma_f16_2sm(d_tmem, a_desc + 2 * k, b_desc + 2 * k, p.idesc_main_t,
+                           (kb | k) != 0 ? 1u : 0u);
+            umma_commit_2sm(&empty_bar[s], 3);
+          }
+          __syncwarp();
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      };
+      auto tail = [&](int st) {
+        mbar_wait(&full_bar[s], ph, S2_MMA_TAIL_FULL);
+        tc_fence_after_sync();
+        const uint64_t b_desc =
+            make_desc_sw128(smem_u32(stage_base + (size_t)s * stg_bytes + A_TILE_BYTES));
+        if (elect_one()) {
+          for (int k = 0; k < p.tail_ksteps; ++k)
+            umma_f16_2sm(tmem_base + st * ACC_STRIDE, t_desc + 2 * k, b_desc + 2 * k, p.idesc_tail, 1u);
+          umma_commit_2sm(&empty_bar[s], 3);
+          umma_commit_2sm(&accfull_bar[st], 3);
+        }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+      };
+      int it = 0;
+      int e = 0;
+      int n_blk = sc.t0 % p.num_n_blk;          // tracked incrementally: no div/mod per tile
+      int st = 0;                               // TMEM stage of tile `it` and its use parity
+      uint32_t st_par = 0;
+      for (int tile = sc.t0; tile < sc.t1;) {
+        const bool nm = tile == sc.t0 || n_blk == 0;
+        const bool lk = nm && tile + 1 < sc.t1 && n_blk + 1 != p.num_n_blk;
+        if (lane == 0) TS2(2, it, 0);
+        mbar_wait(&accempty_bar[st], st_par ^ 1, S2_MMA_ACC_EMPTY);
+        tc_fence_after_sync();
+        if (lane == 0) TS2(2, it, 1);
+        if (nm && e > 0 && elect_one()) umma_commit_2sm(st_free_bar, 3);
+        __syncwarp();
+        main_loop(st);
+        if (lane == 0) TS2(2, it, 2);
+        if (nm && elect_one()) umma_commit_2sm(tfull_bar, 3);
+        __syncwarp();
+        int st2 = st + 1;
+        uint32_t par2 = st_par;
+        if (st2 == NST) { st2 = 0; par2 ^= 1; }
+        if (lk) {
+          mbar_wait(&accempty_bar[st2], par2 ^ 1, S2_MMA_ACC_EMPTY);
+          tc_fence_after_sync();
+          main_loop(st2);
+          if (lane == 0) TS2(2, it, 3);
+        }
+        if (nm) {
+          mbar_wait(tsm_full_bar, e & 1, S2_MMA_TSM);
+          tc_fence_after_sync();
+          ++e;
+        }
+        if (lane == 0) TS2(2, it, 4);
+        tail(st);
+        if (lk) tail(st2);
+        if (lane == 0) TS2(2, it, 5);
+        if (DBG && lane == 0 && (int)blockIdx.x == p.dbg_cta && it < 32) { p.dbg[2 * 256 + it * 8 + 6] = wsum + 1; wsum = 0; }
+        const int adv = lk ? 2 : 1;
+        for (int a = 0; a < adv; ++a) {
+          if (++st == NST) { st = 0; st_par ^= 1; }
+          if (++n_blk == p.num_n_blk) n_blk = 0;
+        }
+        it += adv;
+        tile += adv;
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // =============================== T step (both CTAs, own rows) =====================
+    const int qd = warp & 3;
+    const int row = qd * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    const uint32_t trow = smem_u32(t_tile) + row * 128;
+    const int sw = row & 7;
+    const uint32_t tsm0 = mapa_shared(smem_u32(tsm_full_bar), 0);
+    TIO* t_out = reinterpret_cast<TIO*>(p.T_out);
+    int it = 0, e = 0;
+    for (int tile = sc.t0; tile < sc.t1; ++tile, ++it) {
+      if (!sc.new_m(tile)) continue;
+      const int n_blk = tile % p.num_n_blk;
+      const int m_blk = tile / p.num_n_blk;
+      const int st = it % NST;
+      const long long gm = (long long)m_blk * 256 + rank * BM + row;
+      if (threadIdx.x == 128) TS2(3, it, 0);
+      mbar_wait(tfull_bar, e & 1, S2_T_TFULL);
+      tc_fence_after_sync();
+      if (threadIdx.x == 128) TS2(3, it, 1);
+      uint32_t tv[16];
+      tmem_ld_x16(tmem_base + lane_addr + st * ACC_STRIDE + BN, tv);
+      tmem_ld_wait();
+      if (t_out != nullptr && n_blk == 0 && gm < p.M) {
+        TIO* dst = t_out + gm * p.r;
+        if (p.r == 4) {
+          uint2 q;
+          q.x = pack2b<TIO>(__uint_as_float(tv[0]), __uint_as_float(tv[1]));
+          q.y = pack2b<TIO>(__uint_as_float(tv[2]), __uint_as_float(tv[3]));
+          *reinterpret_cast<uint2*>(dst) = q;
+        } else if (p.r == 8 || p.r == 16) {
+          uint4 q;
+          q.x = pack2b<TIO>(__uint_as_float(tv[0]), __uint_as_float(tv[1]));
+          q.y = pack2b<TIO>(__uint_as_float(tv[2]), __uint_as_float(tv[3]));
+          q.z = pack2b<TIO>(__uint_as_float(tv[4]), __uint_as_float(tv[5]));
+          q.w = pack2b<TIO>(__uint_as_float(tv[6]), __uint_as_float(tv[7]));
+          *reinterpret_cast<uint4*>(dst) = q;
+          if (p.r == 16) {
+            q.x = pack2b<TIO>(__uint_as_float(tv[8]), __uint_as_float(tv[9]));
+            q.y = pack2b<TIO>(__uint_as_float(tv[10]), __uint_as_float(tv[11]));
+            q.z = pack2b<TIO>(__uint_as_float(tv[12]), __uint_as_float(tv[13]));
+            q.w = pack2b<TIO>(__uint_as_float(tv[14]), __uint_as_float(tv[15]));
+            *reinterpret_cast<uint4*>(dst + 8) = q;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j < p.r) dst[j] = TIO(__uint_as_float(tv[j]));
+        }
+      }
+      float tf[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        tf[j] = __uint_as_float(tv[j]) * p.scale;
+        if (p.has_bias && j == p.r) tf[j] = 1.0f;
+      }
+      if (e > 0) mbar_wait(st_free_bar, (e - 1) & 1, S2_T_FREE);
+      st_shared_v4(trow + ((0 ^ sw) << 4), pack2b<TIO>(tf[0], tf[1]), pack2b<TIO>(tf[2], tf[3]),
+                   pack2b<TIO>(tf[4], tf[5]), pack2b<TIO>(tf[6], tf[7]));
+      st_shared_v4(trow + ((1 ^ sw) << 4), pack2b<TIO>(tf[8], tf[9]), pack2b<TIO>(tf[10], tf[11]),
+                   pack2b<TIO>(tf[12], tf[13]), pack2b<TIO>(tf[14], tf[15]));
+      if (p.tail_ksteps > 1) {
+        st_shared_v4(trow + ((2 ^ sw) << 4), pack2b<TIO>(1.0f, 0.f), 0u, 0u, 0u);
+        st_shared_v4(trow + ((3 ^ sw) << 4), 0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before_sync();
+      mbar_arrive_cluster(tsm0);
+      if (threadIdx.x == 128) TS2(3, it, 2);
+      ++e;
+    }
+  } else if (warp >= 8) {
+    // =============================== epilogue (both CTAs, own rows) ===================
+    const int ew = warp - 8;
+    const int qd = warp & 3;
+    const int half = ew >> 2;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    uint8_t* my_staging = staging + ew * (2 * 32 * EPI_COLS * 2);
+    const uint32_t stg_row = smem_u32(my_staging) + lane * 64;
+    const int wr_sw = (lane >> 1) & 3;
+    const int n_units = BN / EPI_COLS;
+    int it = 0;
+    uint32_t buf = 0;
+    for (int tile = sc.t0; tile < sc.t1; ++tile, ++it) {
+      const int n_blk = tile % p.num_n_blk;
+      const int m_blk = tile / p.num_n_blk;
+      const int st = it % NST;
+      const uint32_t acc_addr = tmem_base + lane_addr + st * ACC_STRIDE;
+      if (lane == 0 && qd == 0) TS2(4 + half, it, 0);
+      mbar_wait(&accfull_bar[st], (it / NST) & 1, S2_EPI_ACC);
+      tc_fence_after_sync();
+      if (lane == 0 && qd == 0) TS2(4 + half, it, 1);
+      uint32_t v[2][32];
+      auto live = [&](int c) { return c < n_units && n_blk * BN + c * EPI_COLS < p.Nout; };
+      if (live(half)) tmem_ld_x32(acc_addr + half * EPI_COLS, v[0]);
+#pragma unroll
+      for (int ci = 0; ci < MAX_CI; ++ci) {
+        const int c = 2 * ci + half;
+        if (live(c)) {
+          tmem_ld_wait_dep(v[ci & 1]);
+          if (ci + 1 < MAX_CI && live(c + 2))
+            tmem_ld_x32(acc_addr + (c + 2) * EPI_COLS, v[(ci + 1) & 1]);
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          const uint32_t dst = stg_row + buf * (32 * EPI_COLS * 2);
+          const uint32_t* w = v[ci & 1];
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            st_shared_v4(dst + ((q ^ wr_sw) << 4),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 0]), __uint_as_float(w[q * 8 + 1])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 2]), __uint_as_float(w[q * 8 + 3])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 4]), __uint_as_float(w[q * 8 + 5])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 6]), __uint_as_float(w[q * 8 + 7])));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmY, my_staging + buf * (32 * EPI_COLS * 2), n_blk * BN + c * EPI_COLS,
+                         m_blk * 256 + (int)rank * BM + qd * 32);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        }
+      }
+      // this warp's TMEM reads of the stage are complete: one arrival per warp on the leader
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&accempty_bar[st]), 0));
+      if (lane == 0 && qd == 0) TS2(4 + half, it, 2);
+    }
+    if (lane == 0) tma_store_wait_all<0>();
+    if (lane == 0 && qd == 0) TS2(4 + half, 31, 7);
+  }
+
+  // =============================== teardown ===========================================
+  tc_fence_before_sync();
+  cluster_sync_all();      // no CTA leaves while its pair may still touch its smem / barriers
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc_2sm(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+int tc2_smem_bytes(int BN, int* stages_out) {
+  const int budget = 232448 - 1024;
+  int stages = (budget - tc2::fixed_bytes()) / tc2::stage_bytes(BN);
+  if (stages > tc2::MAX_STAGES) stages = tc2::MAX_STAGES;
+  if (stages_out) *stages_out = stages;
+  return stages * tc2::stage_bytes(BN) + tc2::fixed_bytes() + 1024;
+}
+
+template <typename TIO, bool DBG>
+static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmWa,
+                                   const CUtensorMap& tmWb, const CUtensorMap& tmS1,
+                                   const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p,
+                                   int smem_bytes, cudaStream_t stream) {
+  auto kern = lora_gemm_tc2_kernel<TIO, DBG>;
+  // per (kernel, smem) state: the opt-in smem size and how many PAIRS can be co-resident
+  static thread_local int configured_smem = 0;
+  static thread_local int max_clusters = 0;
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(tc2::NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (configured_smem != smem_bytes) {
+    cudaError_t e =
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return e;
+    cfg.gridDim = dim3(2, 1, 1);
+    int n = 0;
+    e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+    if (e != cudaSuccess) return e;
+    if (n < 1) return cudaErrorInvalidConfiguration;
+    max_clusters = n;
+    configured_smem = smem_bytes;
+  }
+  const int num_tiles = p.num_m_blk * p.num_n_blk;
+  const int ncl = num_tiles < max_clusters ? num_tiles : max_clusters;
+  cfg.gridDim = dim3(2 * ncl, 1, 1);
+  return cudaLaunchKernelEx(&cfg, kern, tmX, tmWa, tmWb, tmS1, tmS2, tmY, p);
+}
+
+template <typename TIO>
+cudaError_t launch_tc2(const CUtensorMap& tmX, const CUtensorMap& tmWa, const CUtensorMap& tmWb,
+                       const CUtensorMap& tmS1, const CUtensorMap& tmS2, const CUtensorMap& tmY,
+                       const TcParams& p, int smem_bytes, cudaStream_t stream) {
+  if (p.dbg != nullptr)
+    return launch_tc2_impl<TIO, true>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
+  return launch_tc2_impl<TIO, false>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
+}
+
+template cudaError_t launch_tc2<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&,
+                                               const CUtensorMap&, const CUtensorMap&,
+                                               const CUtensorMap&, const CUtensorMap&,
+                                               const TcParams&, int, cudaStream_t);
+template cudaError_t launch_tc2<__half>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                        const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                        const TcParams&, int, cudaStream_t);
+
+}  // namespace b200

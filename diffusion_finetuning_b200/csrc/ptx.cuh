@@ -241,10 +241,13 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
   return r;
 }
-// arrive (release, cluster scope) on an mbarrier given by its shared::cluster address
+// arrive on an mbarrier given by its shared::cluster address (the peer CTA's barrier).
+// Default .release.cta semantics on purpose: a cluster-scope release compiles to MEMBAR.ALL.GPU
+// (and a cluster-scope acquire wait to CCTL.IVALL) per call, which doubled the kernel time.  No
+// generic-proxy data crosses the pair here: what the peer publishes is smem for the tensor core
+// (fence.proxy.async before the arrive) and drained TMEM (tcgen05.wait::ld + fence before it).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr)
-               : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;

@@ -45,5 +45,8 @@ for role in range(6):
         cells = []
         for k in range(8):
             v = int(row[k])
-            if v: cells.append(f"{keys[role][k] if k < len(keys[role]) else 'k%d' % k}={(v - t0) / 1.9e3:7.2f}us")
+            if v and role == 2 and k == 6:
+                cells.append(f"operand_wait={v / 1.9e3:5.2f}us")
+            elif v:
+                cells.append(f"{keys[role][k] if k < len(keys[role]) else 'k%d' % k}={(v - t0) / 1.9e3:7.2f}us")
         print(f"{names[role]:9s} it={it:2d} " + " ".join(cells))
