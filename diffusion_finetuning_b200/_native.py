@@ -40,6 +40,12 @@ SIGNATURES = {
     "b200lora_lora_grads": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32,
                                    _i32, _i32, _vp, _i64, _vp]),
     "b200lora_lora_grads_workspace": (_i64, [_i64, _i32, _i32, _i32]),
+    "b200lora_conv2d_repack_weight": (_i32, [_vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_conv2d_pack_lora": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _vp, _vp, _i32, _i32, _i32, _i32,
+                                         _i32, _i32, _vp]),
+    "b200lora_conv2d_gemm": (_i32, [_vp, _vp, _i32, _vp, _vp, _f32, _vp, _vp] + [_i32] * 15 + [_vp]),
+    "b200lora_conv2d_zcat": (_i32, [_vp, _vp, _i32, _f32, _vp, _vp, _i64, _i32, _i32, _i32, _vp]),
+    "b200lora_conv2d_grad_a": (_i32, [_vp, _vp, _f32, _vp] + [_i32] * 14 + [_vp]),
     "b200lora_merge": (_i32, [_vp, _vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_absmean_accum": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_svd_epilogue": (_i32, [_vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _vp]),
@@ -81,6 +87,7 @@ def dtype_code(dt):
 # number of successful C-ABI kernel launches since import (every entry point that computes is
 # exactly one kernel launch); bench.py reports the delta over its timed region as `gpu_launches`
 LAUNCHES = 0
+_DEBUG_ERR = os.environ.get("B200LORA_DEBUG_ERR", "0") == "1"
 
 
 def check(rc, what):
@@ -89,6 +96,10 @@ def check(rc, what):
         msg = lib().b200lora_last_error().decode(errors="replace")
         raise B200LoraError(f"{what} failed with code {rc}: {msg}")
     LAUNCHES += 1
+    if _DEBUG_ERR:
+        code = lib().b200lora_peek_cuda_error()
+        if code != 0:
+            raise B200LoraError(f"{what} returned 0 but left CUDA error {code} pending")
 
 
 def stream_ptr(device):

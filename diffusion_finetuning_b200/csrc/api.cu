@@ -33,6 +33,12 @@ int tc2_smem_bytes(int BN, int* stages_out);
 template <typename TIO>
 cudaError_t launch_tc2(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                        const CUtensorMap&, const CUtensorMap&, const TcParams&, int, cudaStream_t);
+cudaError_t launch_conv_repack(const void*, int, void*, int, int, int, int, int, int, int, cudaStream_t);
+cudaError_t launch_conv_pack(const void*, const void*, int, const void*, int, void*, void*, void*, int,
+                             int, int, int, int, int, int, int, int, cudaStream_t);
+cudaError_t launch_conv_zcat(const void*, const void*, int, float, void*, void*, long long, int, int,
+                             int, int, int, cudaStream_t);
+cudaError_t launch_conv_dA(const void*, const void*, float, float*, const int*, int, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
                         int, int, int, int, cudaStream_t);
 template <typename TIO>
@@ -137,6 +143,48 @@ static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t c
   return 0;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                   cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeIm2colFn get_im2col_fn() {
+  static EncodeIm2colFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(p);
+  });
+  return fn;
+}
+
+// NHWC activations [N,H,W,C] (16-bit) as an im2col-mode map: 128 pixels x 64 channels per load,
+// base pixels restricted to [-pad, dim + pad - (filter-1)*dil) so that base + tap offset covers
+// exactly the padded window; out-of-image elements are zero-filled by the TMA unit.
+static int get_tmap_im2col(CUtensorMap* out, const void* ptr, int N, int H, int W, int C, int R, int S,
+                           int str_h, int str_w, int pad_h, int pad_w, int dil_h, int dil_w, int dt) {
+  EncodeIm2colFn fn = get_im2col_fn();
+  if (!fn) { set_error("cuTensorMapEncodeIm2col entry point not available"); return B200LORA_E_CUDA; }
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {-pad_w, -pad_h};
+  int upper[2] = {pad_w - (S - 1) * dil_w, pad_h - (R - 1) * dil_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)str_w, (cuuint32_t)str_h, 1};
+  CUtensorMapDataType cdt =
+      dt == B200LORA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult rc = fn(out, cdt, 4, const_cast<void*>(ptr), gdim, gstr, lower, upper, 64, 128, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeIm2col failed rc=%d (N=%d H=%d W=%d C=%d R=%d S=%d)", (int)rc, N, H, W,
+              C, R, S);
+    return B200LORA_E_CUDA;
+  }
+  return 0;
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // can the tcgen05 path take this problem?  (writes the reason to the error slot if not)
@@ -211,12 +259,19 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
 }
 
 // CTA-pair variant (linear_tc2.cu): same math, tcgen05 cta_group::2, 256-row blocks per pair
+struct ConvGeoH { int N, H, W, C, Ho, Wo, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w; };
+
 static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, bool has_bias,
                    const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
                    void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, const ConvGeoH* cg = nullptr) {
   TcParams p;
   memset(&p, 0, sizeof(p));
+  if (cg) {
+    p.conv = 1; p.cv_S = cg->S; p.cv_cpb = (cg->C + 63) / 64; p.cv_Ho = cg->Ho; p.cv_Wo = cg->Wo;
+    p.cv_pad_h = cg->pad_h; p.cv_pad_w = cg->pad_w; p.cv_str_h = cg->str_h; p.cv_str_w = cg->str_w;
+    p.cv_dil_h = cg->dil_h; p.cv_dil_w = cg->dil_w;
+  }
   p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
   p.BN = tc_pick_bn(Nout);
   p.num_m_blk = (int)((M + 255) / 256);
@@ -240,8 +295,11 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
 
   CUtensorMap tmX, tmWa, tmWb, tmS1, tmS2, tmY;
   int rc;
-  if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
-                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if (cg) {
+    if ((rc = get_tmap_im2col(&tmX, X, cg->N, cg->H, cg->W, cg->C, cg->R, cg->S, cg->str_h, cg->str_w,
+                              cg->pad_h, cg->pad_w, cg->dil_h, cg->dil_w, io_dtype))) return rc;
+  } else if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
+                            CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmWa, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)(H - 16), 64,
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmWb, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)H, 64, io_dtype,
@@ -256,7 +314,7 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
                       ? launch_tc2<__nv_bfloat16>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream)
                       : launch_tc2<__half>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream);
   if (e != cudaSuccess) {
-    set_error("tc2 launch failed: %s", cudaGetErrorString(e));
+    if (!g_err[0]) set_error("tc2 launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
   }
   return 0;
@@ -307,6 +365,9 @@ extern "C" int b200lora_tc_supported(void) {
 }
 // diagnostic: non-zero if the tensor-core kernel's watchdog fired (site<<16 | block)
 extern "C" unsigned int b200lora_watchdog_code(void) { return tc_read_watchdog(); }
+
+// diagnostic: the CUDA runtime's pending (sticky-until-read) error code, without clearing it
+extern "C" int b200lora_peek_cuda_error(void) { return (int)cudaPeekAtLastError(); }
 
 // diagnostic, not part of the drop-in surface: trace CTA `cta` of the next tcgen05 launches
 extern "C" void b200lora_debug_timeline(void* buf, int cta) {
@@ -367,8 +428,10 @@ extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int
       if (impl == B200LORA_IMPL_TC) return B200LORA_E_ARG;
     }
     if (ok)
-      return (use_pair() ? run_tc2 : run_tc)(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale,
-                                             Y, ldy, T_out, M, Kc, Nout, r, io_dtype, stream);
+      return use_pair() ? run_tc2(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale, Y, ldy,
+                                  T_out, M, Kc, Nout, r, io_dtype, stream)
+                        : run_tc(X, ldx, W, ldw, bias != nullptr, S1_pack, S2_pack, scale, Y, ldy,
+                                 T_out, M, Kc, Nout, r, io_dtype, stream);
     if (impl == B200LORA_IMPL_TC) {
       if (io_dtype == B200LORA_F32) return B200LORA_E_DTYPE;
       DevInfo di = dev_info();
@@ -407,6 +470,99 @@ extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layou
   const void* s2p = pk ? pk + 2ll * (16 * ((int64_t)K + N) + 64ll * N) : nullptr;
   return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, s1p, A, 1, K, ab_dtype,
                             s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+}
+
+// =========================================================================================
+// LoRA-Conv2d (implicit GEMM over NHWC activations)
+// =========================================================================================
+static int conv_out(int in, int k, int st, int pad, int dil) { return (in + 2 * pad - dil * (k - 1) - 1) / st + 1; }
+
+extern "C" int b200lora_conv2d_repack_weight(const void* W_oihw, int w_dtype, void* out, int Cout,
+                                             int Cin, int R, int S, int mode, int io_dtype,
+                                             b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!W_oihw || !out) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(w_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) { set_error("bad dtype"); return B200LORA_E_DTYPE; }
+  if (mode != 0 && mode != 1) { set_error("bad mode"); return B200LORA_E_ARG; }
+  // forward rows are padded to 64 input channels; backward rows to 64 output channels + the 64 LoRA columns
+  const int Cp = mode == 0 ? (Cin + 63) / 64 * 64 : (Cout + 63) / 64 * 64 + 64;
+  cudaError_t e = launch_conv_repack(W_oihw, w_dtype, out, Cout, Cin, R, S, Cp, mode, io_dtype,
+                                     reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("conv repack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_conv2d_pack_lora(const void* A, const void* B, int ab_dtype, const void* bias,
+                                         int bias_dtype, void* A_pack, void* Bn_pack, void* Wb,
+                                         int Cout, int Cin, int R, int S, int r, int io_dtype,
+                                         b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!A || !B || !A_pack || !Bn_pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype)) ||
+      (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) { set_error("bad dtype"); return B200LORA_E_DTYPE; }
+  if (r < 1 || r > 16) { set_error("conv pack: needs 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  const int Cp = (Cin + 63) / 64 * 64, Coutp = (Cout + 63) / 64 * 64, Cz = Coutp + 64;
+  cudaError_t e = launch_conv_pack(A, B, ab_dtype, bias, bias_dtype, A_pack, Bn_pack, Wb, Cout, Cin, R, S,
+                                   Cp, Coutp, Cz, r, io_dtype, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("conv pack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_conv2d_gemm(const void* X_nhwc, const void* Wk, int has_bias, const void* S1_pack,
+                                    const void* S2_pack, float scale, void* Y_nhwc, void* T_out, int N,
+                                    int H, int W, int C, int Cout, int R, int S, int str_h, int str_w,
+                                    int pad_h, int pad_w, int dil_h, int dil_w, int r, int io_dtype,
+                                    b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!X_nhwc || !Wk || !S1_pack || !S2_pack || !Y_nhwc) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("conv2d: 16-bit io only"); return B200LORA_E_DTYPE; }
+  if (N < 1 || H < 1 || W < 1 || C < 1 || Cout < 1 || R < 1 || S < 1 || str_h < 1 || str_w < 1 ||
+      dil_h < 1 || dil_w < 1 || pad_h < 0 || pad_w < 0 || r < 1 || r > 16) { set_error("conv2d: bad shape"); return B200LORA_E_SHAPE; }
+  if ((C % 8) || (Cout % 8)) { set_error("conv2d: channel counts must be multiples of 8"); return B200LORA_E_ALIGN; }
+  if (!aligned16(X_nhwc) || !aligned16(Wk) || !aligned16(Y_nhwc) || !aligned16(S1_pack) || !aligned16(S2_pack)) {
+    set_error("conv2d: pointers must be 16-byte aligned"); return B200LORA_E_ALIGN;
+  }
+  DevInfo di = dev_info();
+  if (!di.ok || di.major != 10) { set_error("conv2d needs an sm_100 device"); return B200LORA_E_ARCH; }
+  ConvGeoH g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.R = R; g.S = S; g.str_h = str_h; g.str_w = str_w;
+  g.pad_h = pad_h; g.pad_w = pad_w; g.dil_h = dil_h; g.dil_w = dil_w;
+  g.Ho = conv_out(H, R, str_h, pad_h, dil_h);
+  g.Wo = conv_out(W, S, str_w, pad_w, dil_w);
+  if (g.Ho < 1 || g.Wo < 1) { set_error("conv2d: empty output"); return B200LORA_E_SHAPE; }
+  const long long M = (long long)N * g.Ho * g.Wo;
+  const int Kc = R * S * ((C + 63) / 64 * 64);
+  return run_tc2(X_nhwc, 0, Wk, Kc, has_bias != 0, S1_pack, S2_pack, scale, Y_nhwc, Cout, T_out, M, Kc,
+                 Cout, r, io_dtype, reinterpret_cast<cudaStream_t>(stream_), &g);
+}
+
+extern "C" int b200lora_conv2d_zcat(const void* dY, const void* B, int ab_dtype, float scale, void* Z,
+                                    void* dT, int64_t M, int Cout, int r, int io_dtype,
+                                    b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!dY || !B || !Z || !dT) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(ab_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) { set_error("bad dtype"); return B200LORA_E_DTYPE; }
+  if (Cout % 8 || r < 1 || r > 16) { set_error("zcat: Cout %% 8 == 0 and 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  if (M <= 0) return 0;
+  const int Coutp = (Cout + 63) / 64 * 64;
+  cudaError_t e = launch_conv_zcat(dY, B, ab_dtype, scale, Z, dT, M, Cout, Coutp, Coutp + 64, r, io_dtype,
+                                   reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("zcat launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float scale, float* dA, int N, int H,
+                                  int W, int C, int R, int S, int str_h, int str_w, int pad_h, int pad_w,
+                                  int dil_h, int dil_w, int r, int io_dtype, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!X_nhwc || !dT || !dA) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("conv2d_dA: 16-bit io only"); return B200LORA_E_DTYPE; }
+  if (C % 8 || r < 1 || r > 16) { set_error("conv2d_dA: C %% 8 == 0 and 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  int geo[14] = {N, H, W, C, conv_out(H, R, str_h, pad_h, dil_h), conv_out(W, S, str_w, pad_w, dil_w), R, S,
+                 str_h, str_w, pad_h, pad_w, dil_h, dil_w};
+  cudaError_t e = launch_conv_dA(X_nhwc, dT, scale, dA, geo, r, io_dtype, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("conv2d_dA launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
 }
 
 extern "C" int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r) {

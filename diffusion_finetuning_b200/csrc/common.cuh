@@ -46,6 +46,10 @@ struct TcParams {
   float scale;
   void* T_out;
   unsigned idesc_main, idesc_main_t, idesc_tail;
+  // implicit-GEMM convolution (conv != 0): X is NHWC, the k-block index walks (tap, 64-channel
+  // block); rows are output pixels in (n, oh, ow) order
+  int conv, cv_S, cv_cpb, cv_Ho, cv_Wo;
+  int cv_pad_h, cv_pad_w, cv_str_h, cv_str_w, cv_dil_h, cv_dil_w;
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;
 };

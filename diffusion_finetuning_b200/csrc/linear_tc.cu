@@ -24,6 +24,8 @@
 //                swizzled smem staging -> TMA store (bounds clipped by the tensor map)
 // Accumulators are multi-buffered in TMEM (2-4 stages): the epilogue of tile i overlaps the main
 // loops of the following tiles.
+#include <mutex>
+
 #include "ptx.cuh"
 #include "common.cuh"
 
@@ -460,19 +462,20 @@ cudaError_t launch_tc(const CUtensorMap& tmX, const CUtensorMap& tmW, const CUte
   const int grid = num_tiles < num_sms ? num_tiles : num_sms;
   if (p.dbg != nullptr) {   // timeline build (tools/timeline.py)
     auto dk = lora_gemm_tc_kernel<TIO, true>;
-    cudaError_t e = cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    cudaError_t e = cudaFuncSetAttribute(dk, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     if (e != cudaSuccess) return e;
     dk<<<grid, tc::NUM_THREADS, smem_bytes, stream>>>(tmX, tmW, tmS1, tmS2, tmY, p);
     return cudaGetLastError();
   }
   auto kern = lora_gemm_tc_kernel<TIO, false>;
-  static thread_local int configured_smem = 0;
-  if (configured_smem < smem_bytes) {
-    cudaError_t e =
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    if (e != cudaSuccess) return e;
-    configured_smem = smem_bytes;
-  }
+  // process-wide attribute: raise it once to the device maximum (a per-thread cache would let the
+  // autograd thread lower the cap under the main thread)
+  static std::once_flag cap_once;
+  static cudaError_t cap_err = cudaSuccess;
+  std::call_once(cap_once, [&] {
+    cap_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  });
+  if (cap_err != cudaSuccess) return cap_err;
   kern<<<grid, tc::NUM_THREADS, smem_bytes, stream>>>(tmX, tmW, tmS1, tmS2, tmY, p);
   return cudaGetLastError();
 }

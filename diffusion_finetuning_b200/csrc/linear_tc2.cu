@@ -21,7 +21,8 @@
 //                the leader's barrier through shared::cluster
 //   warps 8-15   epilogue for the CTA's own 128 rows: pipelined tcgen05.ld -> staging -> TMA store
 // A pair owns a contiguous range of (256-row block, n-tile) pairs in n-fastest order.
-#include <cooperative_groups.h>
+#include <map>
+#include <mutex>
 
 #include "ptx.cuh"
 #include "common.cuh"
@@ -173,6 +174,17 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       const uint32_t full0_base = mapa_shared(smem_u32(&full_bar[0]), 0);   // leader's full_bar[0]
       auto load_main = [&](int n_blk, int m_blk) {
         const int n0 = n_blk * BN;
+        // convolution: first output pixel of this CTA's 128 rows -> (image, oh, ow)
+        int cv_n = 0, cv_h = 0, cv_w = 0;
+        if (p.conv) {
+          const long long m0 = (long long)m_blk * 256 + (long long)rank * BM;
+          const int hw = p.cv_Ho * p.cv_Wo;
+          cv_n = (int)(m0 / hw);
+          const int rem = (int)(m0 - (long long)cv_n * hw);
+          cv_h = (rem / p.cv_Wo) * p.cv_str_h - p.cv_pad_h;
+          cv_w = (rem % p.cv_Wo) * p.cv_str_w - p.cv_pad_w;
+        }
+        int tap = 0, cb = 0;
         for (int kb = 0; kb < p.num_k_blk; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);
           uint8_t* a_dst = stage_base + (size_t)s * stg_bytes;
@@ -182,7 +194,12 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             if (xrole) {
               if (leader) mbar_arrive_expect_tx(&full_bar[s], main_tx);
               else mbar_arrive_cluster(full0);
-              tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
+              if (p.conv)
+                tma_load_im2col_2sm(a_dst, &tmX, full0, cb * BK, cv_w, cv_h, cv_n,
+                                    (uint16_t)((tap % p.cv_S) * p.cv_dil_w),
+                                    (uint16_t)((tap / p.cv_S) * p.cv_dil_h), pol_x);
+              else
+                tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
               tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);                  // H rows
@@ -192,6 +209,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             }
           }
           __syncwarp();
+          if (++cb == p.cv_cpb) { cb = 0; ++tap; }
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       };
@@ -481,9 +499,12 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
                                    const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p,
                                    int smem_bytes, cudaStream_t stream) {
   auto kern = lora_gemm_tc2_kernel<TIO, DBG>;
-  // per (kernel, smem) state: the opt-in smem size and how many PAIRS can be co-resident
-  static thread_local int configured_smem = 0;
-  static thread_local int max_clusters = 0;
+  // The opt-in smem cap is a process-wide attribute of the function: raise it ONCE to the device
+  // maximum (autograd runs the backward on another thread — a per-thread cache of "what I last
+  // set" let one thread lower the cap under the other).  Co-resident pair count is cached per smem.
+  static std::mutex mu;
+  static bool cap_raised = false;
+  static std::map<int, int> clusters_for_smem;
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -495,22 +516,33 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
   cfg.stream = stream;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (configured_smem != smem_bytes) {
-    cudaError_t e =
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    if (e != cudaSuccess) return e;
-    cfg.gridDim = dim3(2, 1, 1);
-    int n = 0;
-    e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
-    if (e != cudaSuccess) return e;
-    if (n < 1) return cudaErrorInvalidConfiguration;
-    max_clusters = n;
-    configured_smem = smem_bytes;
+  int max_clusters = 0;
+  {
+    std::lock_guard<std::mutex> g(mu);
+    if (!cap_raised) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+      if (e != cudaSuccess) { set_error("tc2: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return e; }
+      cap_raised = true;
+    }
+    auto it = clusters_for_smem.find(smem_bytes);
+    if (it == clusters_for_smem.end()) {
+      cfg.gridDim = dim3(2, 1, 1);
+      int n = 0;
+      cudaError_t e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+      if (e != cudaSuccess) { set_error("tc2: cudaOccupancyMaxActiveClusters(smem=%d): %s", smem_bytes, cudaGetErrorString(e)); return e; }
+      if (n < 1) return cudaErrorInvalidConfiguration;
+      it = clusters_for_smem.emplace(smem_bytes, n).first;
+    }
+    max_clusters = it->second;
   }
   const int num_tiles = p.num_m_blk * p.num_n_blk;
   const int ncl = num_tiles < max_clusters ? num_tiles : max_clusters;
   cfg.gridDim = dim3(2 * ncl, 1, 1);
-  return cudaLaunchKernelEx(&cfg, kern, tmX, tmWa, tmWb, tmS1, tmS2, tmY, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmX, tmWa, tmWb, tmS1, tmS2, tmY, p);
+  if (e != cudaSuccess)
+    set_error("tc2: cudaLaunchKernelEx(grid=%d, smem=%d, BN=%d, stages=%d): %s", 2 * ncl, smem_bytes, p.BN,
+              p.stages, cudaGetErrorString(e));
+  return e;
 }
 
 template <typename TIO>

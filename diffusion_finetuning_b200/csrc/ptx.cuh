@@ -286,6 +286,19 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap
       "l"(cache_policy)
       : "memory");
 }
+// im2col-mode 4-D load (NHWC activations): 128 consecutive output pixels x 64 channels starting
+// at base pixel (w, h, n) (input coordinates of filter tap (0,0)), shifted by the tap offsets
+__device__ __forceinline__ void tma_load_im2col_2sm(void* smem_dst, const void* tmap,
+                                                    uint32_t bar_cluster_addr, int32_t c, int32_t w,
+                                                    int32_t h, int32_t n, uint16_t off_w,
+                                                    uint16_t off_h, uint64_t cache_policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".L2::cache_hint [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8}, %9;\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c), "r"(w), "r"(h), "r"(n),
+      "h"(off_w), "h"(off_h), "l"(cache_policy)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_alloc_2sm(uint32_t* dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
                    smem_u32(dst_smem)),

@@ -138,6 +138,42 @@ int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layout,
                            int io_dtype, int impl, b200lora_stream_t stream);
 
 /*
+ * LoRA-Conv2d — `conv(x) + lora_up(lora_down(x)) * scale` with lora_down a conv of the same
+ * geometry to r channels and lora_up a 1x1 conv.  NOT in the reference snapshot (lora.py has only
+ * LoraInjectedLinear); upstream cloneofsimo/lora `LoraInjectedConv2d` semantics, SURVEY §8(c).
+ * Implicit GEMM over NHWC activations: rows = output pixels (n, oh, ow), K = (kh, kw, 64-channel
+ * blocks) fetched by TMA im2col loads, same tcgen05 CTA-pair kernel as the linear layer.
+ *   Cp = ceil(Cin/64)*64, Coutp = ceil(Cout/64)*64, Cz = Coutp + 64.
+ *
+ * repack_weight  W [Cout,Cin,R,S] (OIHW) -> mode 0: Wk [Cout, R*S*Cp] (forward operand)
+ *                                          mode 1: Wb [Cin,  R*S*Cz] (backward operand: flipped,
+ *                                                  transposed; LoRA columns filled by pack_lora)
+ * pack_lora      A [r,Cin,R,S], B [Cout,r], bias -> A_pack [16, R*S*Cp], Bn_pack [Cout,64] and
+ *                (Wb != NULL) the A-columns of Wb
+ * gemm           Y[N,Ho,Wo,Cout] = conv(X; Wk) + bias + (s·T)·S2ᵀ,  T = conv(X; S1) -> T_out [M,r]
+ *                (backward dX: X = Z from zcat, Wk = Wb, zero packs, pad' = (R-1)*dil - pad)
+ * zcat           backward: dT = dY·B [M,r] and Z [M,Cz] = [dY | 0 | s·dT | 0]
+ * dA             backward: dA[r,Cin,R,S] (fp32, ADDED into) += s·Σ_m dT[m,:]ᵀ · im2col(X)[m,:]
+ * dB uses b200lora_lora_grads(dY, NULL, T, NULL, ..., dA = NULL, dB).
+ */
+int b200lora_conv2d_repack_weight(const void* W_oihw, int w_dtype, void* out, int Cout, int Cin,
+                                  int R, int S, int mode, int io_dtype, b200lora_stream_t stream);
+int b200lora_conv2d_pack_lora(const void* A, const void* B, int ab_dtype, const void* bias,
+                              int bias_dtype, void* A_pack, void* Bn_pack, void* Wb /*nullable*/,
+                              int Cout, int Cin, int R, int S, int r, int io_dtype,
+                              b200lora_stream_t stream);
+int b200lora_conv2d_gemm(const void* X_nhwc, const void* Wk, int has_bias, const void* S1_pack,
+                         const void* S2_pack, float scale, void* Y_nhwc, void* T_out /*nullable*/,
+                         int N, int H, int W, int C, int Cout, int R, int S, int stride_h,
+                         int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int r,
+                         int io_dtype, b200lora_stream_t stream);
+int b200lora_conv2d_zcat(const void* dY, const void* B, int ab_dtype, float scale, void* Z, void* dT,
+                         int64_t M, int Cout, int r, int io_dtype, b200lora_stream_t stream);
+int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float scale, float* dA, int N, int H,
+                       int W, int C, int R, int S, int stride_h, int stride_w, int pad_h, int pad_w,
+                       int dil_h, int dil_w, int r, int io_dtype, b200lora_stream_t stream);
+
+/*
  * Token reductions for the LoRA gradients — replaces the autograd of lora.py:50:
  *   dB[n,j] (+)= s · Σ_m dY[m,n]·T[m,j]      [N,r]
  *   dA[j,k] (+)= s · Σ_m dT[m,j]·X[m,k]      [r,K]
