@@ -22,7 +22,7 @@ void set_error(const char* fmt, ...) {
 }
 
 // forward declarations of the per-file launchers
-int tc_pick_bn(int Nout);
+int tc_pick_bn(long long M, int Kc, int Nout, int rows, int units);
 int tc_smem_bytes(int BN, int* stages_out);
 void tc_tmem_plan(int BN, int* nst, int* stride);
 unsigned int tc_read_watchdog();
@@ -47,8 +47,9 @@ cudaError_t launch_simt(const void*, long long, const void*, long long, int, con
                         float, void*, long long, void*, long long, int, int, int, cudaStream_t);
 template <typename T>
 cudaError_t launch_lora_grads(const void*, const void*, const void*, const void*, float, float*,
-                              float*, float*, float*, long long, int, int, int, cudaStream_t);
-int grad_reduce_splits(long long M, int C, int esize);
+                              float*, float*, float*, long long, int, int, int, const CUtensorMap*,
+                              const CUtensorMap*, int, cudaStream_t);
+int grad_reduce_splits(long long M, int C, int C_other, int esize, int sms);
 template <typename TW, typename TL, int MODE>
 cudaError_t launch_merge(const void*, void*, const void*, const void*, float, int, int, int,
                          float*, cudaStream_t);
@@ -214,7 +215,7 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
-  p.BN = tc_pick_bn(Nout);
+  p.BN = tc_pick_bn(M, Kc, Nout, 128, dev_info().sms);
   p.num_m_blk = (int)((M + 127) / 128);
   p.num_n_blk = (Nout + p.BN - 1) / p.BN;
   p.num_k_blk = (Kc + 63) / 64;
@@ -273,7 +274,7 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
     p.cv_dil_h = cg->dil_h; p.cv_dil_w = cg->dil_w;
   }
   p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
-  p.BN = tc_pick_bn(Nout);
+  p.BN = tc_pick_bn(M, Kc, Nout, 256, dev_info().sms / 2);
   p.num_m_blk = (int)((M + 255) / 256);
   p.num_n_blk = (Nout + p.BN - 1) / p.BN;
   p.num_k_blk = (Kc + 63) / 64;
@@ -567,14 +568,16 @@ extern "C" int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float 
 
 extern "C" int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r) {
   const int RP = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
-  // worst case over element sizes (fp32 has the narrowest column tile -> most column blocks,
-  // 16-bit the most splits); take the max of both
+  int sms = dev_info().sms;
+  if (sms <= 0) sms = 148;
+  // worst case over element sizes and over which of dA / dB the call asks for
   int64_t best = 0;
-  for (int es = 2; es <= 4; es += 2) {
-    const int64_t a = (int64_t)grad_reduce_splits(M, K, es) * K * RP * 4;
-    const int64_t b = (int64_t)grad_reduce_splits(M, N, es) * N * RP * 4;
-    if (a + b > best) best = a + b;
-  }
+  for (int es = 2; es <= 4; es += 2)
+    for (int both = 0; both < 2; ++both) {
+      const int64_t a = (int64_t)grad_reduce_splits(M, K, both ? N : 0, es, sms) * K * RP * 4;
+      const int64_t b = (int64_t)grad_reduce_splits(M, N, both ? K : 0, es, sms) * N * RP * 4;
+      if (a + b > best) best = a + b;
+    }
   return best + 256;
 }
 
@@ -587,9 +590,12 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
   if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
   if (r < 1 || r > 16) { set_error("lora_grads supports 1 <= r <= 16 (got %d)", r); return B200LORA_E_SHAPE; }
   if (M <= 0) return 0;
+  if (!dA && !dB) return 0;
   const int vec = 16 / dtype_size(io_dtype);
   if ((dB && (N % vec)) || (dA && (K % vec))) { set_error("lora_grads needs N and K multiples of %d", vec); return B200LORA_E_ALIGN; }
   if ((dB && (!dY || !T)) || (dA && (!X || !dT))) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  DevInfo di = dev_info();
+  const int sms = di.sms > 0 ? di.sms : 148;
   float* partA = nullptr;
   float* partB = nullptr;
   if (deterministic) {
@@ -599,10 +605,25 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
     }
     const int RP = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
     partA = reinterpret_cast<float*>(workspace);
-    partB = partA + (int64_t)grad_reduce_splits(M, K, dtype_size(io_dtype)) * K * RP;
+    partB = partA + (dA ? (int64_t)grad_reduce_splits(M, K, dB ? N : 0, dtype_size(io_dtype), sms) * K * RP : 0);
+  }
+  // 16-bit io: tensor-pipe reduction fed by TMA ([128 tokens x 64 columns] boxes)
+  CUtensorMap tmDY, tmX;
+  const CUtensorMap* pDY = nullptr;
+  const CUtensorMap* pX = nullptr;
+  if (io_dtype != B200LORA_F32) {
+    if (!di.ok || di.major != 10) { set_error("lora_grads (16-bit io) needs an sm_100 device"); return B200LORA_E_CUDA; }
+    if ((dB && !aligned16(dY)) || (dA && !aligned16(X))) { set_error("lora_grads needs 16-byte aligned dY / X"); return B200LORA_E_ALIGN; }
+    int rc;
+    if (dB && (rc = get_tmap(&tmDY, dY, (uint64_t)M, (uint64_t)N, (uint64_t)N, 128, 64, io_dtype,
+                             CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    if (dA && (rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)K, (uint64_t)K, 128, 64, io_dtype,
+                             CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    pDY = dB ? &tmDY : &tmX;
+    pX = dA ? &tmX : &tmDY;
   }
   cudaError_t e = cudaSuccess;
-#define RUN(T_) e = launch_lora_grads<T_>(dY, X, T, dT, scale, dA, dB, partA, partB, M, K, N, r, stream)
+#define RUN(T_) e = launch_lora_grads<T_>(dY, X, T, dT, scale, dA, dB, partA, partB, M, K, N, r, pDY, pX, sms, stream)
   if (io_dtype == B200LORA_F32) RUN(float);
   else if (io_dtype == B200LORA_F16) RUN(__half);
   else RUN(__nv_bfloat16);

@@ -421,20 +421,32 @@ lora_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-int tc_pick_bn(int Nout) {
+// Tile width: minimise  waves x (MMA columns x k-blocks + fixed per-tile cost)  over the candidate
+// widths.  `rows` = output rows per tile (128 single CTA, 256 CTA pair), `units` = CTAs or pairs
+// that run concurrently.  The fixed cost (tail MMA hand-off, accumulator switch, epilogue drain;
+// ~0.45 us measured against 1.03 us for 176 columns x 5 k-blocks) is what makes wide tiles win on
+// wide layers even when they leave a ragged last tile.
+int tc_pick_bn(long long M, int Kc, int Nout, int rows, int units) {
   const char* env = getenv("B200LORA_BN");
   if (env) {
     int v = atoi(env);
     if (v >= 32 && v <= 224 && v % 32 == 0) return v;
   }
-  // prefer the largest tile <= 224 that divides Nout; fall back to 128 (ragged last tile)
-  const int cands[] = {160, 128, 192, 224, 96, 64};
-  for (int c : cands)
-    if (Nout % c == 0) return c;
   if (Nout <= 32) return 32;
   if (Nout <= 64) return 64;
-  if (Nout <= 96) return 96;
-  return 128;
+  const int cands[] = {160, 128, 192, 224, 96, 64};   // ties go to the earlier entry
+  const double kb = (double)((Kc + 63) / 64) + 0.25;
+  const double fixed = 385.0;
+  const long long mb = (M + rows - 1) / rows;
+  int best = 128;
+  double best_cost = 1e300;
+  for (int c : cands) {
+    const long long tiles = mb * ((Nout + c - 1) / c);
+    const long long waves = (tiles + units - 1) / units;
+    const double cost = (double)waves * ((c + 16) * kb + fixed);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = c; }
+  }
+  return best;
 }
 
 // TMEM accumulator stages for a tile of BN (+16 rank) columns, and their column stride

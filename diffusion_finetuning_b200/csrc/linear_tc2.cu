@@ -123,6 +123,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   const int NST = p.nst;
   const int ACC_STRIDE = p.acc_stride;
   if (threadIdx.x == 0) TS2(0, 0, 0);
+  pdl_launch_dependents();   // the next launch may run its prologue (below) under this grid's tail
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX);
@@ -153,6 +154,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   cluster_sync_all();       // peer barriers initialised before any remote arrive / multicast commit
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();               // nothing above reads or writes global memory of earlier kernels
   if (threadIdx.x == 0) TS2(0, 0, 1);
 
   if (warp == 0 || warp == 3) {
@@ -493,6 +495,16 @@ int tc2_smem_bytes(int BN, int* stages_out) {
   return stages * tc2::stage_bytes(BN) + tc2::fixed_bytes() + 1024;
 }
 
+// B200LORA_PDL=0 turns programmatic dependent launch off (A/B measurements)
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200LORA_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 template <typename TIO, bool DBG>
 static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmWa,
                                    const CUtensorMap& tmWb, const CUtensorMap& tmS1,
@@ -506,16 +518,18 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
   static bool cap_raised = false;
   static std::map<int, int> clusters_for_smem;
   cudaLaunchConfig_t cfg = {};
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.blockDim = dim3(tc2::NUM_THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = stream;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   int max_clusters = 0;
   {
     std::lock_guard<std::mutex> g(mu);

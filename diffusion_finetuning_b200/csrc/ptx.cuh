@@ -76,6 +76,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
   }
 }
 
+// ------------------------------- programmatic dependent launch --------------------------
+// launch_dependents: the next kernel in the stream (if launched with the programmatic-serialization
+// attribute) may start its prologue while this grid is still running; wait: block until every
+// prerequisite grid has completed and its writes are visible.  Both are no-ops otherwise.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+}
+
 // ------------------------------- fences -------------------------------------------------
 // generic-proxy writes to smem -> visible to the async proxy (TMA store, tcgen05.mma reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {

@@ -7,9 +7,22 @@
 // instruction, and 4 such loads are kept in flight per thread.  Partial sums go lane -> warp
 // (shuffle) -> CTA (smem) -> either fp32 atomics into the gradient accumulator (default) or a
 // [splits, C, RP] workspace reduced by a second kernel (deterministic mode).
+//
+// 16-bit io takes the tensor-pipe variant below (lora_grad_mma_kernel): the SIMT kernel needs
+// r/2 FMA per byte plus conversions, which at r = 4 is ~70 % of the SM's issue slots at full HBM
+// rate -- it measured 1-2 TB/s.  The variant streams [128 tokens x 64 columns] boxes with TMA
+// (128-byte swizzle) through a 4-stage mbarrier ring and contracts over tokens with
+// ldmatrix.trans + mma.sync m16n8k16 (2 instructions per 512 bytes), so the kernel is bound by
+// HBM, not by issue.  fp32 io (the correctness mode) keeps the SIMT kernel.
+#include <cuda.h>
+#include <mutex>
+
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
+
+bool pdl_enabled();   // linear_tc2.cu
 
 namespace red {
 constexpr int NT = 256;
@@ -163,6 +176,200 @@ __global__ void lora_grad_finalize_kernel(const RedProblem p0, const RedProblem 
   p.out[c * p.out_cs + j * p.out_js] += s * scale;
 }
 
+// ------------------------------------------------------------------------------------------
+// tensor-pipe variant (16-bit io)
+// ------------------------------------------------------------------------------------------
+namespace rtc {
+constexpr int TOK = 128;                     // tokens per stage: 16 per consumer warp
+constexpr int COLS = 64;                     // columns per CTA strip = one 128-byte swizzle row
+constexpr int STAGE_BYTES = TOK * COLS * 2;  // 16 KB
+constexpr int NS = 4;                        // stages in flight per CTA (3 CTAs per SM)
+constexpr int CONSUMERS = 8;
+constexpr int NT = (CONSUMERS + 1) * 32;
+constexpr int SMEM_BYTES = NS * STAGE_BYTES + 1024;
+constexpr int CTAS_PER_SM = 3;
+}
+
+template <typename T>
+__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4],
+                                                         uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};\n"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma_16816<__half>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                                  uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};\n"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// B fragment of P[tok0 .. tok0+16, 8*jh .. 8*jh+8): lane (g = lane/4, t = lane%4) holds
+// (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero
+__device__ __forceinline__ void load_p_frag(const unsigned short* __restrict__ P, long long tok0,
+                                            int j, int r, long long M, int t, uint32_t (&b)[2]) {
+  b[0] = 0u; b[1] = 0u;
+  if (j < r) {
+    const long long k0 = tok0 + 2 * t;
+    if (k0 + 9 < M) {
+      const unsigned short* q = P + k0 * r + j;
+      b[0] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + r) << 16);
+      b[1] = (uint32_t)__ldg(q + 8 * r) | ((uint32_t)__ldg(q + 9 * r) << 16);
+    } else {
+      uint32_t e[4];
+      const int off[4] = {0, 1, 8, 9};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) e[i] = (k0 + off[i] < M) ? (uint32_t)__ldg(P + (k0 + off[i]) * r + j) : 0u;
+      b[0] = e[0] | (e[1] << 16);
+      b[1] = e[2] | (e[3] << 16);
+    }
+  }
+}
+
+struct RedTcGeom {
+  long long M;
+  int rows_per_block;   // multiple of rtc::TOK
+  int blocks0, r, rp;   // rp: rank stride of the deterministic workspace (4 / 8 / 16)
+  float scale;
+};
+
+template <typename T, int NJ>
+__global__ void __launch_bounds__(rtc::NT)
+lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
+                     const RedProblem p0, const RedProblem p1, const RedTcGeom g) {
+  extern __shared__ uint8_t red_smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[rtc::NS];
+  __shared__ __align__(8) uint64_t empty_bar[rtc::NS];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(red_smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+
+  const bool second = (int)blockIdx.x >= g.blocks0;
+  const RedProblem& p = second ? p1 : p0;
+  const CUtensorMap* tm = second ? &tm1 : &tm0;
+  const int bid = second ? blockIdx.x - g.blocks0 : blockIdx.x;
+  const int cb = bid % p.col_blocks;
+  const int sp = bid / p.col_blocks;
+  const long long m_begin = (long long)sp * g.rows_per_block;
+  long long m_end = m_begin + g.rows_per_block;
+  if (m_end > g.M) m_end = g.M;
+  const int nstage = (int)((m_end - m_begin + rtc::TOK - 1) / rtc::TOK);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < rtc::NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], rtc::CONSUMERS); }
+    fence_mbar_init();
+    tma_prefetch_desc(tm);
+  }
+  __syncthreads();
+  pdl_wait();   // dY / X / T / dT come from the kernels before this one
+
+  if (warp == rtc::CONSUMERS) {
+    // ------------------------------ producer: one box per stage ------------------------------
+    const uint64_t pol = policy_evict_first();
+    for (int it = 0; it < nstage; ++it) {
+      const int s = it % rtc::NS;
+      if (it >= rtc::NS) mbar_wait(&empty_bar[s], ((it / rtc::NS) - 1) & 1, 40);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&full_bar[s], rtc::STAGE_BYTES);
+        tma_load_2d(smem + s * rtc::STAGE_BYTES, tm, &full_bar[s], cb * rtc::COLS,
+                    (int)(m_begin + (long long)it * rtc::TOK), pol);
+      }
+      __syncwarp();
+    }
+    return;
+  }
+
+  // ------------------------------ consumers: 16 tokens per warp ------------------------------
+  const int gq = lane >> 2, tq = lane & 3;
+  const unsigned short* __restrict__ P = reinterpret_cast<const unsigned short*>(p.P);
+  float acc[4][NJ][4];
+#pragma unroll
+  for (int ct = 0; ct < 4; ++ct)
+#pragma unroll
+    for (int jh = 0; jh < NJ; ++jh)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[ct][jh][i] = 0.f;
+
+  // ldmatrix.trans row address of this lane: matrix mi = lane/8 -> (token half, column chunk parity)
+  const int mi = lane >> 3, rr = lane & 7;
+  const uint32_t row_off = (uint32_t)((warp * 16 + rr + ((mi >> 1) << 3)) * 128);
+  const uint32_t smem_base = smem_u32(smem);
+
+  uint32_t bnext[NJ][2];
+#pragma unroll
+  for (int jh = 0; jh < NJ; ++jh) load_p_frag(P, m_begin + warp * 16, gq + 8 * jh, g.r, g.M, tq, bnext[jh]);
+
+  for (int it = 0; it < nstage; ++it) {
+    const int s = it % rtc::NS;
+    uint32_t bcur[NJ][2];
+#pragma unroll
+    for (int jh = 0; jh < NJ; ++jh) { bcur[jh][0] = bnext[jh][0]; bcur[jh][1] = bnext[jh][1]; }
+    if (it + 1 < nstage) {
+#pragma unroll
+      for (int jh = 0; jh < NJ; ++jh)
+        load_p_frag(P, m_begin + (long long)(it + 1) * rtc::TOK + warp * 16, gq + 8 * jh, g.r, g.M, tq, bnext[jh]);
+    }
+    mbar_wait(&full_bar[s], (it / rtc::NS) & 1, 41);
+    const uint32_t st_addr = smem_base + s * rtc::STAGE_BYTES + row_off;
+#pragma unroll
+    for (int ct = 0; ct < 4; ++ct) {
+      uint32_t a[4];
+      const uint32_t addr = st_addr + ((uint32_t)((2 * ct + (mi & 1)) ^ rr) << 4);
+      asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+                   : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3])
+                   : "r"(addr));
+#pragma unroll
+      for (int jh = 0; jh < NJ; ++jh) mma_16816<T>(acc[ct][jh], a, bcur[jh][0], bcur[jh][1]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty_bar[s]);
+  }
+
+  // ------------------------------ CTA reduction over the 8 token groups ----------------------
+  constexpr int JW = 8 * NJ;
+  float* red = reinterpret_cast<float*>(smem);   // [8 warps][64 cols][JW]; the ring is drained
+  named_bar_sync(1, rtc::CONSUMERS * 32);
+#pragma unroll
+  for (int ct = 0; ct < 4; ++ct)
+#pragma unroll
+    for (int jh = 0; jh < NJ; ++jh) {
+      float* dst = red + ((warp * rtc::COLS + ct * 16 + gq) * JW + jh * 8 + 2 * tq);
+      *reinterpret_cast<float2*>(dst) = make_float2(acc[ct][jh][0], acc[ct][jh][1]);
+      *reinterpret_cast<float2*>(dst + 8 * JW) = make_float2(acc[ct][jh][2], acc[ct][jh][3]);
+    }
+  named_bar_sync(1, rtc::CONSUMERS * 32);
+  for (int idx = threadIdx.x; idx < rtc::COLS * JW; idx += rtc::CONSUMERS * 32) {
+    const int c = idx / JW, j = idx % JW;
+    const int gc = cb * rtc::COLS + c;
+    if (gc >= p.C || j >= g.r) continue;
+    float sum = 0.f;
+#pragma unroll
+    for (int w = 0; w < rtc::CONSUMERS; ++w) sum += red[(w * rtc::COLS + c) * JW + j];
+    if (p.partial != nullptr) p.partial[((long long)sp * p.C + gc) * g.rp + j] = sum;
+    else atomicAdd(p.out + gc * p.out_cs + j * p.out_js, sum * g.scale);
+  }
+}
+
+// rows per CTA (multiple of 128) so that both problems together fill ~3 CTAs per SM
+static int tc_rows_per_block(long long M, int C0, int C1, int sms) {
+  const long long stages = (M + rtc::TOK - 1) / rtc::TOK;
+  const long long cbs = (C0 + rtc::COLS - 1) / rtc::COLS + (C1 + rtc::COLS - 1) / rtc::COLS;
+  const long long slots = (long long)sms * rtc::CTAS_PER_SM;
+  long long spb = (cbs * stages + slots - 1) / slots;
+  if (spb < 1) spb = 1;
+  if (spb > stages) spb = stages;
+  return (int)(spb * rtc::TOK);
+}
+
 static int pick_splits(long long M, int col_blocks) {
   long long target = (148 * 4 + col_blocks - 1) / col_blocks;
   long long max_splits = (M + 127) / 128;
@@ -172,7 +379,13 @@ static int pick_splits(long long M, int col_blocks) {
   return (int)target;
 }
 
-int grad_reduce_splits(long long M, int C, int esize) {
+// Row splits of the problem over C columns when it runs together with a problem over C_other
+// columns (0 = alone).  Sizes the deterministic workspace; must match launch_lora_grads.
+int grad_reduce_splits(long long M, int C, int C_other, int esize, int sms) {
+  if (esize == 2) {
+    const int rows = tc_rows_per_block(M, C, C_other, sms);
+    return (int)((M + rows - 1) / rows);
+  }
   const int CT = 8 * (16 / esize);
   return pick_splits(M, (C + CT - 1) / CT);
 }
@@ -191,11 +404,81 @@ static void fill_problem(RedProblem& p, const void* Z, long long ldz, const void
   p.splits = (int)((M + rpb - 1) / rpb);
 }
 
+template <typename T>
+static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* tmX, const void* Tm,
+                                   const void* dT, float scale, float* dA, float* dB, float* partA,
+                                   float* partB, long long M, int K, int N, int r, int sms,
+                                   cudaStream_t stream) {
+  RedProblem pb = {}, pa = {};
+  RedTcGeom g = {};
+  g.M = M; g.r = r; g.scale = scale;
+  g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  g.rows_per_block = tc_rows_per_block(M, dB ? N : 0, dA ? K : 0, sms);
+  const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
+  int nb = 0, na = 0;
+  if (dB) {
+    pb.P = Tm; pb.out = dB; pb.out_cs = r; pb.out_js = 1; pb.partial = partB; pb.C = N;
+    pb.col_blocks = (N + rtc::COLS - 1) / rtc::COLS; pb.splits = splits; pb.rows_per_block = g.rows_per_block;
+    nb = pb.col_blocks * splits;
+  }
+  if (dA) {
+    pa.P = dT; pa.out = dA; pa.out_cs = 1; pa.out_js = K; pa.partial = partA; pa.C = K;
+    pa.col_blocks = (K + rtc::COLS - 1) / rtc::COLS; pa.splits = splits; pa.rows_per_block = g.rows_per_block;
+    na = pa.col_blocks * splits;
+  }
+  g.blocks0 = nb;
+  const CUtensorMap& m0 = dB ? *tmDY : *tmX;   // an absent problem never dereferences its map
+  const CUtensorMap& m1 = dA ? *tmX : *tmDY;
+  cudaError_t e = cudaSuccess;
+#define LAUNCH_TC(NJ_)                                                                           \
+  do {                                                                                           \
+    auto kern = lora_grad_mma_kernel<T, NJ_>;                                                    \
+    static std::once_flag once;                                                                  \
+    static cudaError_t cap = cudaSuccess;                                                        \
+    std::call_once(once, [&] {                                                                   \
+      cap = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, rtc::SMEM_BYTES); \
+    });                                                                                          \
+    if (cap != cudaSuccess) return cap;                                                          \
+    cudaLaunchConfig_t cfg = {};                                                                 \
+    cudaLaunchAttribute attr[1];                                                                 \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                             \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                      \
+    cfg.gridDim = dim3(nb + na, 1, 1);                                                           \
+    cfg.blockDim = dim3(rtc::NT, 1, 1);                                                          \
+    cfg.dynamicSmemBytes = rtc::SMEM_BYTES;                                                      \
+    cfg.stream = stream;                                                                         \
+    cfg.attrs = attr;                                                                            \
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;                                                        \
+    e = cudaLaunchKernelEx(&cfg, kern, m0, m1, pb, pa, g);                                       \
+    if (e != cudaSuccess) return e;                                                              \
+  } while (0)
+  if (r <= 8) LAUNCH_TC(1); else LAUNCH_TC(2);
+#undef LAUNCH_TC
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  if ((partA && dA) || (partB && dB)) {
+    const int n0 = dB ? N * g.rp : 0, n1 = dA ? K * g.rp : 0;
+    const int blocks = (n0 + n1 + 255) / 256;
+    if (g.rp == 4) lora_grad_finalize_kernel<4><<<blocks, 256, 0, stream>>>(pb, pa, n0, r, scale);
+    else if (g.rp == 8) lora_grad_finalize_kernel<8><<<blocks, 256, 0, stream>>>(pb, pa, n0, r, scale);
+    else lora_grad_finalize_kernel<16><<<blocks, 256, 0, stream>>>(pb, pa, n0, r, scale);
+    e = cudaGetLastError();
+  }
+  return e;
+}
+
 // Both gradient reductions in one launch.  dB <- (dY, T), dA <- (X, dT); either may be skipped.
+// tmDY / tmX: [M,N] / [M,K] tensor maps with a [128 x 64] box (16-bit io); null selects the SIMT
+// kernel (fp32 io).
 template <typename T>
 cudaError_t launch_lora_grads(const void* dY, const void* X, const void* Tm, const void* dT,
                               float scale, float* dA, float* dB, float* partA, float* partB,
-                              long long M, int K, int N, int r, cudaStream_t stream) {
+                              long long M, int K, int N, int r, const CUtensorMap* tmDY,
+                              const CUtensorMap* tmX, int sms, cudaStream_t stream) {
+  if constexpr (sizeof(T) == 2) {
+    if (tmDY != nullptr && tmX != nullptr)
+      return launch_grads_tc<T>(tmDY, tmX, Tm, dT, scale, dA, dB, partA, partB, M, K, N, r, sms, stream);
+  }
   RedProblem pb = {}, pa = {};
   int nb = 0, na = 0;
   if (dB) { fill_problem(pb, dY, N, Tm, dB, /*cs=*/r, /*js=*/1, partB, M, N, sizeof(T)); nb = pb.col_blocks * pb.splits; }
@@ -217,13 +500,16 @@ cudaError_t launch_lora_grads(const void* dY, const void* X, const void* Tm, con
 
 template cudaError_t launch_lora_grads<float>(const void*, const void*, const void*, const void*,
                                               float, float*, float*, float*, float*, long long,
-                                              int, int, int, cudaStream_t);
+                                              int, int, int, const CUtensorMap*, const CUtensorMap*,
+                                              int, cudaStream_t);
 template cudaError_t launch_lora_grads<__half>(const void*, const void*, const void*, const void*,
                                                float, float*, float*, float*, float*, long long,
-                                               int, int, int, cudaStream_t);
+                                               int, int, int, const CUtensorMap*, const CUtensorMap*,
+                                               int, cudaStream_t);
 template cudaError_t launch_lora_grads<__nv_bfloat16>(const void*, const void*, const void*,
                                                       const void*, float, float*, float*, float*,
                                                       float*, long long, int, int, int,
+                                                      const CUtensorMap*, const CUtensorMap*, int,
                                                       cudaStream_t);
 
 }  // namespace b200

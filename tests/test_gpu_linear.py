@@ -205,3 +205,47 @@ def test_full_size_properties_bf16():
     lhs = (y2.float() - y0.float())
     rhs = 2.0 * (y_tc.float() - y0.float())
     assert rel_err(lhs, rhs) < 5e-2      # branch is ~1e-2 of the output; bf16 rounding of y dominates
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(32768, 320, 640, 4), (5000, 200, 72, 12), (130, 64, 1280, 8)])
+def test_gradient_reductions_all_modes(shape, dtype):
+    """dB = s·dYᵀT, dA = s·dTᵀX through b200lora_lora_grads: atomic and deterministic modes, either
+    output alone, accumulation into a non-zero buffer; the long case makes every CTA wrap its
+    4-stage ring several times.  Reference: fp64 products of the same 16-bit inputs."""
+    M, K, N, r = shape
+    s = 0.5
+    TOL_RED = 1e-4    # fp32 accumulation over up to 32768 tokens (BASELINE bar for 16-bit io: 2e-2)
+    g = torch.Generator(DEV).manual_seed(11)
+    dy = torch.randn(M, N, device=DEV, generator=g).to(dtype)
+    x = torch.randn(M, K, device=DEV, generator=g).to(dtype)
+    T = torch.randn(M, r, device=DEV, generator=g).to(dtype)
+    dT = torch.randn(M, r, device=DEV, generator=g).to(dtype)
+    dB_ref = (s * dy.double().t() @ T.double()).float()
+    dA_ref = (s * dT.double().t() @ x.double()).float()
+    lib, io, st = nat.lib(), nat.dtype_code(dtype), nat.stream_ptr(torch.device(DEV))
+    ws_bytes = int(lib.b200lora_lora_grads_workspace(M, K, N, r))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+
+    def run(want_a, want_b, det, init=0.0):
+        dA = torch.full((r, K), init, dtype=torch.float32, device=DEV)
+        dB = torch.full((N, r), init, dtype=torch.float32, device=DEV)
+        nat.check(lib.b200lora_lora_grads(nat.ptr(dy), nat.ptr(x), nat.ptr(T), nat.ptr(dT), s,
+                                          nat.ptr(dA) if want_a else None, nat.ptr(dB) if want_b else None,
+                                          M, K, N, r, io, int(det), nat.ptr(ws) if det else None,
+                                          ws_bytes if det else 0, st), "grads")
+        torch.cuda.synchronize()
+        return dA, dB
+
+    for det in (False, True):
+        dA, dB = run(True, True, det)
+        assert rel_err(dA, dA_ref) < TOL_RED and rel_err(dB, dB_ref) < TOL_RED, (det, rel_err(dA, dA_ref), rel_err(dB, dB_ref))
+        dA1, dB1 = run(True, False, det)
+        assert rel_err(dA1, dA_ref) < TOL_RED and dB1.abs().max() == 0
+        dA2, dB2 = run(False, True, det)
+        assert rel_err(dB2, dB_ref) < TOL_RED and dA2.abs().max() == 0
+    a0, b0 = run(True, True, True)
+    a1, b1 = run(True, True, True)
+    assert torch.equal(a0, a1) and torch.equal(b0, b1)          # deterministic mode is bit-reproducible
+    dA, dB = run(True, True, False, init=1.0)                   # accumulates, does not overwrite
+    assert rel_err(dA - 1.0, dA_ref) < 1e-4 and rel_err(dB - 1.0, dB_ref) < 1e-4

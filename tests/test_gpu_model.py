@@ -129,3 +129,65 @@ def test_svd_distill_matches_oracle():
     own_hi = torch.quantile(torch.cat([U.flatten(), Vh.flatten()]), 0.99).item()
     assert own_hi > 0
     assert abs(max(U2.abs().max().item(), V2.abs().max().item()) - own_hi) < 1e-6
+
+
+def _clip_pair(r=4, layers=2):
+    """BASELINE config 4's text tower: transformers' CLIPTextModel (ViT-L/14 widths, random init,
+    `layers` encoder layers), LoRA on {"CLIPAttention"} (cli_lora_pti.py:602-606) — once through the
+    oracle on the CPU, once through the CUDA path, same weights."""
+    from transformers import CLIPTextConfig, CLIPTextModel
+    cfg = CLIPTextConfig(vocab_size=1002, hidden_size=768, intermediate_size=3072, num_hidden_layers=layers,
+                         num_attention_heads=12, max_position_embeddings=77)
+    torch.manual_seed(0)
+    ref = CLIPTextModel(cfg)
+    torch.manual_seed(0)
+    ours = CLIPTextModel(cfg)
+    ref.requires_grad_(False)
+    ours.requires_grad_(False)
+    ref_layers = O.inject(ref, {"CLIPAttention"}, r=r)
+    _, names = L.inject_trainable_lora(ours, {"CLIPAttention"}, r=r)
+    our_layers = [m for m in ours.modules() if isinstance(m, L.LoraInjectedLinear)]
+    assert len(ref_layers) == len(our_layers) == 4 * layers == len(names)
+    g = torch.Generator().manual_seed(7)
+    with torch.no_grad():
+        for a, b in zip(ref_layers, our_layers):
+            a.lora_up.weight.normal_(0, 0.02, generator=g)
+            b.lora_up.weight.copy_(a.lora_up.weight)
+            b.lora_down.weight.copy_(a.lora_down.weight)
+    # PTI also trains the placeholder-token rows of the embedding table (cli_lora_pti.py:280)
+    ref.get_input_embeddings().weight.requires_grad_(True)
+    ours.get_input_embeddings().weight.requires_grad_(True)
+    return ref, ours.to(DEV), ref_layers, our_layers
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_config4_clip_text_encoder_matches_oracle(mode):
+    ref, ours, ref_layers, our_layers = _clip_pair()
+    ids = torch.randint(0, 1000, (8, 77), generator=torch.Generator().manual_seed(3))
+    ids[:, 4], ids[:, 5] = 1000, 1001                       # the two placeholder tokens
+    tol_y, tol_g = (1e-4, 1e-3) if mode == "fp32" else (2e-2, 5e-2)
+    from diffusion_finetuning_b200 import _native as nat
+    before = nat.LAUNCHES
+    if mode == "bf16":
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = ours(input_ids=ids.to(DEV)).last_hidden_state
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            yr = ref(input_ids=ids).last_hidden_state
+    else:
+        y = ours(input_ids=ids.to(DEV)).last_hidden_state
+        yr = ref(input_ids=ids).last_hidden_state
+    # a random target: sum(LayerNorm(x)^2) is constant, its gradient would be pure rounding noise
+    target = torch.randn(8, 77, 768, generator=torch.Generator().manual_seed(4))
+    torch.nn.functional.mse_loss(y.float(), target.to(DEV)).backward()
+    torch.nn.functional.mse_loss(yr.float(), target).backward()
+    assert rel_err(y, yr.float()) < tol_y, rel_err(y, yr.float())
+    assert nat.LAUNCHES - before >= 3 * len(our_layers)     # fwd + bwd-dX + reductions per layer, all native
+    worst = 0.0
+    for a, b in zip(ref_layers, our_layers):
+        assert b.lora_up.weight.grad is not None and b.lora_down.weight.grad is not None
+        worst = max(worst, rel_err(b.lora_up.weight.grad, a.lora_up.weight.grad),
+                    rel_err(b.lora_down.weight.grad, a.lora_down.weight.grad))
+    assert worst < tol_g, worst
+    # dX of every layer reaches the embedding table: rows of the placeholder tokens agree
+    ge, gr = ours.get_input_embeddings().weight.grad, ref.get_input_embeddings().weight.grad
+    assert rel_err(ge[1000:1002], gr[1000:1002]) < tol_g
