@@ -167,13 +167,16 @@ class Trainer:
     optimizer over the returned parameter generators -> fwd/bwd/clip/step
     (train_lora_dreambooth.py:595-676, 816-888)."""
 
-    def __init__(self, device, rank_r, autocast=True):
+    def __init__(self, device, rank_r, autocast=True, channels_last=False):
         import itertools
         import diffusion_finetuning_b200 as L
         from diffusion_finetuning_b200 import dp
         from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
         torch.manual_seed(0)                      # same frozen base on every rank
         self.unet = UNet2DConditionModel().to(device)
+        if channels_last:     # stock-PyTorch setting for the frozen convs/norms; the LoRA layers are 2-D GEMMs
+            self.unet.to(memory_format=torch.channels_last)
+        self.channels_last = channels_last
         self.unet.requires_grad_(False)
         params, names = L.inject_trainable_lora(self.unet, ATTN_TARGETS, r=rank_r)
         self.n_layers = len(names)
@@ -190,8 +193,9 @@ class Trainer:
 
     def step(self, b):
         self.arena.zero()
+        lat = b["latents"].contiguous(memory_format=torch.channels_last) if self.channels_last else b["latents"]
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.autocast):
-            pred = self.unet(b["latents"], b["t"], b["ctx"])
+            pred = self.unet(lat, b["t"], b["ctx"])
         loss = F.mse_loss(pred.float(), b["target"].float(), reduction="mean")
         loss.backward()
         self.arena.finish()
@@ -286,7 +290,7 @@ def config_dict(args, batch):
     return {"workload": WORKLOAD, "unet": "SD-1.5 shape (320,640,1280,1280), 2 layers/block, ctx 77x768",
             "lora": f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out", "latents": f"{args.res}x{args.res}",
             "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
-            "optimizer": "AdamW lr 1e-4, clip 1.0",
+            "optimizer": "AdamW lr 1e-4, clip 1.0", "memory_format": getattr(args, "memory_format", "nchw"),
             "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
 
 
@@ -300,6 +304,8 @@ def main():
     ap.add_argument("--res", type=int, default=64)
     ap.add_argument("--rank", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
+                    help="memory format of the frozen stock-PyTorch UNet (the reference scripts use nchw)")
     ap.add_argument("--breakdown", default=None, help="write the per-kernel breakdown JSON here")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -326,7 +332,7 @@ def main():
     from diffusion_finetuning_b200 import ops
     nat.lib()
 
-    tr = Trainer(device, args.rank)
+    tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last")
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
     for i in range(args.warmup):
@@ -339,13 +345,16 @@ def main():
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ops.PROFILER = prof
     l0 = nat.LAUNCHES
     t_dev = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
     launches = nat.LAUNCHES - l0
-    ops.PROFILER = None
     # ---- timed region 2: end to end from pinned host memory, loss read back every step ----
     t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
+    # ---- region 3: the same K steps with CUDA events around every launch of our kernels (roofline);
+    # kept out of region 1 because an event between two launches defeats their programmatic overlap ----
+    ops.PROFILER = prof
+    t_prof = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
+    ops.PROFILER = None
     clk = clocks.stop() if rank == 0 else None
 
     if rank != 0:
@@ -359,15 +368,16 @@ def main():
     for k in ("fwd", "bwd_dx"):
         for f in gemm:
             gemm[f] += summ.get(k, {}).get(f, 0)
-    step_ms = t_dev / args.steps * 1e3
+    step_ms = t_prof / args.steps * 1e3      # shares below are of the profiled steps
     ach_tf = gemm["flops"] / (gemm["ms"] * 1e-3) / 1e12 if gemm["ms"] else 0.0
-    roofline = {"kernel": "lora_gemm_tc_kernel (fused LoRA linear forward + backward-dX launches)",
+    roofline = {"kernel": "lora_gemm_tc2_kernel (fused LoRA linear forward + backward-dX launches, CTA-pair tcgen05)",
                 "bound": "tensor", "achieved": ach_tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
                 "frac": ach_tf / pk["tf_sustained"], "peak_source": pk["src"] + " (sustained bf16)",
                 "traffic": None,
                 "launches_per_step": gemm["launches"] / args.steps,
                 "avg_launch_us": gemm["ms"] * 1e3 / max(1, gemm["launches"]),
                 "share_of_step": gemm["ms"] / args.steps / step_ms,
+                "profiled_ms_per_step": step_ms,
                 "achieved_hbm_gbs": gemm["bytes"] / (gemm["ms"] * 1e-3) / 1e9 if gemm["ms"] else 0.0}
     if "grads" in summ:
         s = summ["grads"]
@@ -377,9 +387,10 @@ def main():
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
-            roofline["traffic"] = json.load(open(traffic_file)).get("lora_gemm_tc_kernel_bytes_per_launch")
+            roofline["traffic"] = json.load(open(traffic_file)).get("lora_gemm_bytes_per_launch")
         except (ValueError, OSError):
             pass
+    step_ms = t_dev / args.steps * 1e3
     bytes_in = sum(v.numel() * v.element_size() for v in host_pool[0].values())
     samples = args.batch * world * args.steps
     line = {"metric": METRIC, "value": samples / t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps,

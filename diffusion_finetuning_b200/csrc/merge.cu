@@ -10,9 +10,10 @@
 namespace b200 {
 
 namespace mrg {
-constexpr int NT = 256;
-constexpr int ROWS_PER_BLOCK = 32;
-constexpr int MAXR = 64;
+constexpr int TX = 32;        // 16-byte vectors along K per block (512 contiguous bytes per row)
+constexpr int TY = 8;         // row lanes
+constexpr int NT = TX * TY;
+constexpr int UNROLL = 4;     // rows in flight per thread
 }
 
 // rounding of the rank-r product follows the reference: (up @ down) is produced in the LoRA
@@ -25,62 +26,86 @@ __device__ __forceinline__ float merged_value(float w, float p, float alpha) {
   return __fadd_rn(w, ap);
 }
 
-template <typename TW, typename TL, int MODE>  // MODE 0 = merge, 1 = abs-sum
+// Block = 32 vectors x 8 row lanes; every thread keeps its RP x VEC slice of `down` in registers and
+// walks rows ty, ty+8, ... of the block's row panel with UNROLL independent 16-byte loads in flight.
+// r > RP (only RP = 16) makes several passes, accumulating through Wout in fp32.
+template <typename TW, typename TL, int MODE, int RP>  // MODE 0 = merge, 1 = abs-sum
 __global__ void __launch_bounds__(mrg::NT)
 lora_merge_kernel(const TW* __restrict__ Win, TW* __restrict__ Wout, const TL* __restrict__ up,
-                  const TL* __restrict__ down, float alpha, int N, int K, int r,
+                  const TL* __restrict__ down, float alpha, int N, int K, int r, int rows_per_block,
                   float* __restrict__ abs_sum) {
   constexpr int VEC = 16 / sizeof(TW);
-  const int kv = blockIdx.x * mrg::NT + threadIdx.x;  // vector index along K
-  const int k0 = kv * VEC;
-  const int n_begin = blockIdx.y * mrg::ROWS_PER_BLOCK;
-  int n_end = n_begin + mrg::ROWS_PER_BLOCK;
+  const int tx = threadIdx.x & (mrg::TX - 1), ty = threadIdx.x / mrg::TX;
+  const int k0 = (blockIdx.x * mrg::TX + tx) * VEC;
+  const int n_begin = blockIdx.y * rows_per_block;
+  int n_end = n_begin + rows_per_block;
   if (n_end > N) n_end = N;
   float local = 0.f;
-  if (k0 < K) {
-    // K % VEC == 0 guaranteed by the host for the vector path
-    for (int j0 = 0; j0 < r || j0 == 0; j0 += 16) {
-      float d[16][VEC];
-      const int jn = (r - j0) < 16 ? (r - j0) : 16;
+  if (k0 < K) {   // K % VEC == 0 guaranteed by the host
+    for (int j0 = 0; j0 < r; j0 += RP) {
+      float d[RP][VEC];
+      const int jn = (r - j0) < RP ? (r - j0) : RP;
 #pragma unroll
-      for (int j = 0; j < 16; ++j)
+      for (int j = 0; j < RP; ++j)
 #pragma unroll
         for (int v = 0; v < VEC; ++v)
           d[j][v] = (j < jn) ? to_f32(down[(long long)(j0 + j) * K + k0 + v]) : 0.f;
-      const bool first = (j0 == 0), last = (j0 + 16 >= r);
-      // r <= 16 (the common case) makes exactly one pass; larger r accumulates through Wout
-      for (int n = n_begin; n < n_end; ++n) {
-        float pacc[VEC];
+      const bool first = (j0 == 0), last = (j0 + RP >= r);
+      const TW* src = first ? Win : Wout;
+      for (int nb = n_begin + ty; nb < n_end; nb += mrg::TY * mrg::UNROLL) {
+        constexpr bool BATCH_U = RP <= 8;     // RP = 16 would not fit the register file batched
+        uint4 raw[mrg::UNROLL];
+        float u[BATCH_U ? mrg::UNROLL : 1][RP];
+        if (MODE == 0) {
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) pacc[v] = 0.f;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          if (j < jn) {
-            const float u = to_f32(up[(long long)n * r + j0 + j]);
-#pragma unroll
-            for (int v = 0; v < VEC; ++v) pacc[v] = fmaf(u, d[j][v], pacc[v]);
+          for (int q = 0; q < mrg::UNROLL; ++q) {
+            const int n = nb + q * mrg::TY;
+            if (n < n_end) raw[q] = *reinterpret_cast<const uint4*>(src + (long long)n * K + k0);
           }
         }
-        if (MODE == 0) {
-          const TW* src = (first ? Win : Wout) + (long long)n * K + k0;
-          uint4 raw = *reinterpret_cast<const uint4*>(src);
-          TW* wv = reinterpret_cast<TW*>(&raw);
-          if (first && last) {
+        if (BATCH_U) {
 #pragma unroll
-            for (int v = 0; v < VEC; ++v)
-              wv[v] = from_f32<TW>(merged_value<TW, TL>(to_f32(wv[v]), pacc[v], alpha));
-          } else {  // r > 16: plain fp32 accumulation of alpha * partial product
+          for (int q = 0; q < mrg::UNROLL; ++q) {
+            const int n = nb + q * mrg::TY;
 #pragma unroll
-            for (int v = 0; v < VEC; ++v)
-              wv[v] = from_f32<TW>(fmaf(alpha, pacc[v], to_f32(wv[v])));
+            for (int j = 0; j < RP; ++j)
+              u[q][j] = (n < n_end && j < jn) ? to_f32(up[(long long)n * r + j0 + j]) : 0.f;
           }
-          *reinterpret_cast<uint4*>(Wout + (long long)n * K + k0) = raw;
-        } else {
+        }
 #pragma unroll
-          for (int v = 0; v < VEC; ++v) local += fabsf(pacc[v]);
+        for (int q = 0; q < mrg::UNROLL; ++q) {
+          const int n = nb + q * mrg::TY;
+          if (n >= n_end) continue;
+          const int uq = BATCH_U ? q : 0;
+          if (!BATCH_U) {
+#pragma unroll
+            for (int j = 0; j < RP; ++j) u[0][j] = (j < jn) ? to_f32(up[(long long)n * r + j0 + j]) : 0.f;
+          }
+          float pacc[VEC];
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) pacc[v] = 0.f;
+#pragma unroll
+          for (int j = 0; j < RP; ++j)
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) pacc[v] = fmaf(u[uq][j], d[j][v], pacc[v]);
+          if (MODE == 0) {
+            TW* wv = reinterpret_cast<TW*>(&raw[q]);
+            if (first && last) {
+#pragma unroll
+              for (int v = 0; v < VEC; ++v)
+                wv[v] = from_f32<TW>(merged_value<TW, TL>(to_f32(wv[v]), pacc[v], alpha));
+            } else {  // r > 16: plain fp32 accumulation of alpha * partial product
+#pragma unroll
+              for (int v = 0; v < VEC; ++v)
+                wv[v] = from_f32<TW>(fmaf(alpha, pacc[v], to_f32(wv[v])));
+            }
+            *reinterpret_cast<uint4*>(Wout + (long long)n * K + k0) = raw[q];
+          } else {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) local += fabsf(pacc[v]);
+          }
         }
       }
-      if (last) break;
     }
   }
   if (MODE == 1) {
@@ -103,9 +128,18 @@ cudaError_t launch_merge(const void* Win, void* Wout, const void* up, const void
                          float alpha, int N, int K, int r, float* abs_sum, cudaStream_t stream) {
   constexpr int VEC = 16 / sizeof(TW);
   const int kvecs = K / VEC;
-  dim3 grid((kvecs + mrg::NT - 1) / mrg::NT, (N + mrg::ROWS_PER_BLOCK - 1) / mrg::ROWS_PER_BLOCK);
-  lora_merge_kernel<TW, TL, MODE><<<grid, mrg::NT, 0, stream>>>(
-      (const TW*)Win, (TW*)Wout, (const TL*)up, (const TL*)down, alpha, N, K, r, abs_sum);
+  const int gx = (kvecs + mrg::TX - 1) / mrg::TX;
+  // row panel per block: as tall as possible (amortises the `down` slice) while >= ~4 blocks per SM
+  int rows = mrg::TY * mrg::UNROLL * 4;
+  while (rows > mrg::TY && (long long)gx * ((N + rows - 1) / rows) < 148 * 4) rows >>= 1;
+  dim3 grid(gx, (N + rows - 1) / rows);
+#define MERGE_LAUNCH(RP_)                                                                        \
+  lora_merge_kernel<TW, TL, MODE, RP_><<<grid, mrg::NT, 0, stream>>>(                            \
+      (const TW*)Win, (TW*)Wout, (const TL*)up, (const TL*)down, alpha, N, K, r, rows, abs_sum)
+  if (r <= 4) MERGE_LAUNCH(4);
+  else if (r <= 8) MERGE_LAUNCH(8);
+  else MERGE_LAUNCH(16);
+#undef MERGE_LAUNCH
   return cudaGetLastError();
 }
 
