@@ -39,6 +39,9 @@ cudaError_t launch_conv_pack(const void*, const void*, int, const void*, int, vo
 cudaError_t launch_conv_zcat(const void*, const void*, int, float, void*, void*, long long, int, int,
                              int, int, int, cudaStream_t);
 cudaError_t launch_conv_dA(const void*, const void*, float, float*, const int*, int, int, cudaStream_t);
+template <typename TIO>
+cudaError_t launch_conv_zcat_tc(const CUtensorMap*, const CUtensorMap*, const void*, int, float, void*, void*,
+                                long long, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
                         int, int, int, int, cudaStream_t);
 template <typename TIO>
@@ -50,6 +53,9 @@ cudaError_t launch_lora_grads(const void*, const void*, const void*, const void*
                               float*, float*, float*, long long, int, int, int, const CUtensorMap*,
                               const CUtensorMap*, int, cudaStream_t);
 int grad_reduce_splits(long long M, int C, int C_other, int esize, int sms);
+template <typename T>
+cudaError_t launch_conv_grad_a_tc(const CUtensorMap*, const void*, float, float*, const int*, int, int,
+                                  cudaStream_t);
 template <typename TW, typename TL, int MODE>
 cudaError_t launch_merge(const void*, void*, const void*, const void*, float, int, int, int,
                          float*, cudaStream_t);
@@ -108,6 +114,19 @@ struct TmKeyHash {
 static std::mutex g_tm_mu;
 static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
 
+// The tensor-map encoders are driver entry points and need the primary context CURRENT on the calling
+// thread; a thread whose first CUDA work is one of our calls (the autograd backward thread) has only
+// had cudaSetDevice, which binds lazily.  One runtime no-op per thread and device does the binding.
+static void bind_context() {
+  static thread_local int bound_dev = -1;
+  int dev = -1;
+  cudaGetDevice(&dev);
+  if (dev != bound_dev) {
+    cudaFree(0);
+    bound_dev = dev;
+  }
+}
+
 // 2-D row-major [rows, cols] 16-bit tensor, box [box_rows, box_cols]
 static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows, uint32_t box_cols, int dt, CUtensorMapSwizzle sw) {
@@ -123,6 +142,7 @@ static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t c
   }
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return B200LORA_E_CUDA; }
+  bind_context();
   cuuint64_t gdim[2] = {cols, rows};
   cuuint64_t gstr[1] = {ld * 2};
   cuuint32_t box[2] = {box_cols, box_rows};
@@ -168,6 +188,7 @@ static int get_tmap_im2col(CUtensorMap* out, const void* ptr, int N, int H, int 
                            int str_h, int str_w, int pad_h, int pad_w, int dil_h, int dil_w, int dt) {
   EncodeIm2colFn fn = get_im2col_fn();
   if (!fn) { set_error("cuTensorMapEncodeIm2col entry point not available"); return B200LORA_E_CUDA; }
+  bind_context();
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
   int lower[2] = {-pad_w, -pad_h};
@@ -546,8 +567,22 @@ extern "C" int b200lora_conv2d_zcat(const void* dY, const void* B, int ab_dtype,
   if (Cout % 8 || r < 1 || r > 16) { set_error("zcat: Cout %% 8 == 0 and 1 <= r <= 16"); return B200LORA_E_SHAPE; }
   if (M <= 0) return 0;
   const int Coutp = (Cout + 63) / 64 * 64;
-  cudaError_t e = launch_conv_zcat(dY, B, ab_dtype, scale, Z, dT, M, Cout, Coutp, Coutp + 64, r, io_dtype,
-                                   reinterpret_cast<cudaStream_t>(stream_));
+  DevInfo di = dev_info();
+  if (!di.ok || di.major != 10) { set_error("zcat needs an sm_100 device"); return B200LORA_E_CUDA; }
+  if (!aligned16(dY) || !aligned16(Z)) { set_error("zcat needs 16-byte aligned dY / Z"); return B200LORA_E_ALIGN; }
+  const int Cz = Coutp + 64;
+  CUtensorMap tmDY, tmZ;
+  int rc;
+  if ((rc = get_tmap(&tmDY, dY, (uint64_t)M, (uint64_t)Cout, (uint64_t)Cout, 128, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if ((rc = get_tmap(&tmZ, Z, (uint64_t)M, (uint64_t)Cz, (uint64_t)Cz, 128, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  cudaError_t e = io_dtype == B200LORA_BF16
+                      ? launch_conv_zcat_tc<__nv_bfloat16>(&tmDY, &tmZ, B, ab_dtype, scale, Z, dT, M, Cout, Coutp, Cz,
+                                                           r, di.sms, stream)
+                      : launch_conv_zcat_tc<__half>(&tmDY, &tmZ, B, ab_dtype, scale, Z, dT, M, Cout, Coutp, Cz, r,
+                                                    di.sms, stream);
   if (e != cudaSuccess) { set_error("zcat launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
@@ -561,8 +596,18 @@ extern "C" int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float 
   if (C % 8 || r < 1 || r > 16) { set_error("conv2d_dA: C %% 8 == 0 and 1 <= r <= 16"); return B200LORA_E_SHAPE; }
   int geo[14] = {N, H, W, C, conv_out(H, R, str_h, pad_h, dil_h), conv_out(W, S, str_w, pad_w, dil_w), R, S,
                  str_h, str_w, pad_h, pad_w, dil_h, dil_w};
-  cudaError_t e = launch_conv_dA(X_nhwc, dT, scale, dA, geo, r, io_dtype, reinterpret_cast<cudaStream_t>(stream_));
-  if (e != cudaSuccess) { set_error("conv2d_dA launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  // tensor-pipe reduction over the im2col view of X (same TMA map as the forward's X operand)
+  DevInfo di = dev_info();
+  if (!di.ok || di.major != 10) { set_error("conv2d_grad_a needs an sm_100 device"); return B200LORA_E_CUDA; }
+  if (!aligned16(X_nhwc)) { set_error("conv2d_grad_a needs a 16-byte aligned X"); return B200LORA_E_ALIGN; }
+  CUtensorMap tmX;
+  int rc = get_tmap_im2col(&tmX, X_nhwc, N, H, W, C, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w, io_dtype);
+  if (rc) return rc;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  cudaError_t e = io_dtype == B200LORA_BF16
+                      ? launch_conv_grad_a_tc<__nv_bfloat16>(&tmX, dT, scale, dA, geo, r, di.sms, stream)
+                      : launch_conv_grad_a_tc<__half>(&tmX, dT, scale, dA, geo, r, di.sms, stream);
+  if (e != cudaSuccess) { set_error("conv2d_grad_a launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

@@ -8,8 +8,11 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
+
+bool pdl_enabled();   // linear_tc2.cu
 
 // ---------------------------------------------------------------------------------------------
 // weights: W [Cout, Cin, R, S] (OIHW, any dtype) -> GEMM B operand in the io dtype
@@ -166,6 +169,184 @@ conv_zcat_kernel(const TIO* __restrict__ dY, const void* __restrict__ B, int ab_
     }
   }
 }
+
+// Tensor-pipe variant (the one that runs): a [128 pixels x 64 channels] box of dY lands in smem by
+// TMA, goes straight back out to Z by a TMA store (the copy costs no thread instructions), and is
+// contracted against Bᵀ (smem, bf16) with ldmatrix + mma.sync into dT; one CTA owns whole pixel rows,
+// so dT needs no atomics.  HBM-bound: reads dY once, writes Z once.
+namespace zc {
+constexpr int TOK = 128, COLS = 64, STAGE_BYTES = TOK * COLS * 2, NS = 6, CONSUMERS = 8;
+constexpr int LAG = 2;   // warp 0 releases a stage LAG iterations late: its TMA store must have read it
+constexpr int NT = (CONSUMERS + 1) * 32;
+}
+
+template <typename TIO>
+__global__ void __launch_bounds__(zc::NT)
+conv_zcat_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmZ,
+                    const void* __restrict__ B, int ab_dtype, float scale, TIO* __restrict__ Z,
+                    TIO* __restrict__ dT, long long M, int Cout, int Coutp, int Cz, int r) {
+  extern __shared__ uint8_t zc_smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[zc::NS];
+  __shared__ __align__(8) uint64_t empty_bar[zc::NS];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(zc_smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int ldb = Coutp + 8;                                       // +16 bytes: conflict-free B fragments
+  TIO* Bt = reinterpret_cast<TIO*>(smem + zc::NS * zc::STAGE_BYTES);   // [16][ldb]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ncb = Coutp / zc::COLS;
+  const int nrb = (int)((M + zc::TOK - 1) / zc::TOK);
+
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < zc::NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], zc::CONSUMERS); }
+    fence_mbar_init();
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmZ);
+  }
+  pdl_wait();
+  // Bᵀ [16][ldb] in the io dtype (rounded as autocast would round B): zero fill, then a coalesced
+  // 16-byte sweep over B [Cout, r] scattered into place
+  for (int i = threadIdx.x; i < 16 * ldb / 8; i += zc::NT)
+    reinterpret_cast<uint4*>(Bt)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  {
+    const int esz = ab_dtype == B200LORA_F32 ? 4 : 2, per = 16 / esz;
+    const int total = Cout * r;
+    if ((reinterpret_cast<uintptr_t>(B) & 15) == 0) {
+      for (int v = threadIdx.x; v * per < total; v += zc::NT) {
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(B) + v);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int e = v * per + q;
+          if (q < per && e < total) {
+            float f;
+            if (ab_dtype == B200LORA_F32) f = reinterpret_cast<const float*>(&raw)[q & 3];
+            else if (ab_dtype == B200LORA_BF16) f = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(&raw)[q]);
+            else f = __half2float(reinterpret_cast<const __half*>(&raw)[q]);
+            Bt[(e % r) * ldb + e / r] = from_f32<TIO>(f);
+          }
+        }
+      }
+    } else {
+      for (int e = threadIdx.x; e < total; e += zc::NT)
+        Bt[(e % r) * ldb + e / r] = from_f32<TIO>(load_as_float(B, ab_dtype, e));
+    }
+  }
+  __syncthreads();
+
+  if (warp == zc::CONSUMERS) {
+    const uint64_t pol = policy_evict_first();
+    int it = 0;
+    for (int rb = blockIdx.x; rb < nrb; rb += gridDim.x)
+      for (int cb = 0; cb < ncb; ++cb, ++it) {
+        const int s = it % zc::NS;
+        if (it >= zc::NS) mbar_wait(&empty_bar[s], ((it / zc::NS) - 1) & 1, 50);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&full_bar[s], zc::STAGE_BYTES);
+          tma_load_2d(smem + s * zc::STAGE_BYTES, &tmDY, &full_bar[s], cb * zc::COLS, rb * zc::TOK, pol);
+        }
+        __syncwarp();
+      }
+    return;
+  }
+
+  const int gq = lane >> 2, tq = lane & 3;
+  const int mi = lane >> 3, rr = lane & 7;
+  const uint32_t row_off = (uint32_t)((warp * 16 + rr + ((mi & 1) << 3)) * 128);
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t* Bt32 = reinterpret_cast<const uint32_t*>(Bt);
+  int it = 0;
+  for (int rb = blockIdx.x; rb < nrb; rb += gridDim.x) {
+    float acc[2][4];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[nt][i] = 0.f;
+    for (int cb = 0; cb < ncb; ++cb, ++it) {
+      const int s = it % zc::NS;
+      mbar_wait(&full_bar[s], (it / zc::NS) & 1, 51);
+      if (warp == 0 && lane == 0) {       // the copy: same tile, straight back out to Z[:, cb*64 ..]
+        fence_proxy_async_smem();
+        tma_store_2d(&tmZ, smem + s * zc::STAGE_BYTES, cb * zc::COLS, rb * zc::TOK);
+        tma_store_commit();
+      }
+      const uint32_t st_addr = smem_base + s * zc::STAGE_BYTES + row_off;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        uint32_t a[4];
+        ldmatrix_x4(a, st_addr + ((uint32_t)((2 * ks + (mi >> 1)) ^ rr) << 4));
+        const int kc = (cb * zc::COLS + ks * 16 + 2 * tq) >> 1;      // uint32 index of the pair
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const uint32_t* brow = Bt32 + ((gq + 8 * nt) * ldb >> 1);
+          mma_16816<TIO>(acc[nt], a, brow[kc], brow[kc + 4]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        if (warp != 0) {
+          mbar_arrive(&empty_bar[s]);
+        } else if (it >= zc::LAG) {      // stores up to iteration it - LAG have finished reading smem
+          tma_store_wait_read<zc::LAG>();
+          mbar_arrive(&empty_bar[(it - zc::LAG) % zc::NS]);
+        }
+      }
+    }
+    // dT (compact, io dtype) and the 64-channel LoRA block of Z: [s·dT | 0]
+    const long long m0 = (long long)rb * zc::TOK + warp * 16;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const long long m = m0 + gq + 8 * h;
+      if (m < M) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const int j = 8 * nt + 2 * tq;
+          const TIO t0 = from_f32<TIO>(acc[nt][2 * h]), t1 = from_f32<TIO>(acc[nt][2 * h + 1]);
+          if (j < r) dT[m * r + j] = t0;
+          if (j + 1 < r) dT[m * r + j + 1] = t1;
+          TIO zz[2] = {from_f32<TIO>(to_f32(t0) * scale), from_f32<TIO>(to_f32(t1) * scale)};
+          *reinterpret_cast<uint32_t*>(Z + m * Cz + Coutp + j) = *reinterpret_cast<uint32_t*>(zz);
+        }
+      }
+    }
+    for (int idx = lane; idx < 16 * 6; idx += 32) {
+      const long long m = m0 + idx / 6;
+      if (m < M) *reinterpret_cast<uint4*>(Z + m * Cz + Coutp + 16 + (idx % 6) * 8) = make_uint4(0, 0, 0, 0);
+    }
+  }
+  if (warp == 0 && lane == 0) tma_store_wait_all<0>();   // (the last LAG stages are never reloaded)
+}
+
+template <typename TIO>
+cudaError_t launch_conv_zcat_tc(const CUtensorMap* tmDY, const CUtensorMap* tmZ, const void* B, int ab_dtype,
+                                float scale, void* Z, void* dT, long long M, int Cout, int Coutp, int Cz, int r,
+                                int sms, cudaStream_t stream) {
+  const int smem = zc::NS * zc::STAGE_BYTES + 16 * (Coutp + 8) * 2 + 1024;
+  auto kern = conv_zcat_tc_kernel<TIO>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) return e;
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;
+  const long long nrb = (M + zc::TOK - 1) / zc::TOK;
+  const int per_sm = smem <= 110 * 1024 ? 2 : 1;   // blocks that fit an SM's shared memory
+  const int grid = (int)(nrb < (long long)sms * per_sm ? nrb : (long long)sms * per_sm);
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(zc::NT, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, *tmDY, *tmZ, B, ab_dtype, scale, (TIO*)Z, (TIO*)dT, M, Cout, Coutp, Cz, r);
+}
+template cudaError_t launch_conv_zcat_tc<__nv_bfloat16>(const CUtensorMap*, const CUtensorMap*, const void*, int,
+                                                        float, void*, void*, long long, int, int, int, int, int,
+                                                        cudaStream_t);
+template cudaError_t launch_conv_zcat_tc<__half>(const CUtensorMap*, const CUtensorMap*, const void*, int, float,
+                                                 void*, void*, long long, int, int, int, int, int, cudaStream_t);
 
 template <typename TIO>
 static cudaError_t zcat_dispatch(const void* dY, const void* B, int ab_dtype, float scale, void* Z,

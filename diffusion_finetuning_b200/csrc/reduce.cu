@@ -190,27 +190,6 @@ constexpr int SMEM_BYTES = NS * STAGE_BYTES + 1024;
 constexpr int CTAS_PER_SM = 3;
 }
 
-template <typename T>
-__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
-template <>
-__device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4],
-                                                         uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-      "{%0,%1,%2,%3};\n"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-template <>
-__device__ __forceinline__ void mma_16816<__half>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
-                                                  uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-      "{%0,%1,%2,%3};\n"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
 // B fragment of P[tok0 .. tok0+16, 8*jh .. 8*jh+8): lane (g = lane/4, t = lane%4) holds
 // (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero
 __device__ __forceinline__ void load_p_frag(const unsigned short* __restrict__ P, long long tok0,
@@ -238,6 +217,8 @@ struct RedTcGeom {
   int rows_per_block;   // multiple of rtc::TOK
   int blocks0, r, rp;   // rp: rank stride of the deterministic workspace (4 / 8 / 16)
   float scale;
+  // problem 1 as a convolution's dA: Z = im2col(X) [M, taps * cpb * 64], never materialised
+  int conv, cv_S, cv_cpb, cv_C, cv_Ho, cv_Wo, cv_pad_h, cv_pad_w, cv_str_h, cv_str_w, cv_dil_h, cv_dil_w;
 };
 
 template <typename T, int NJ>
@@ -274,14 +255,28 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
 
   if (warp == rtc::CONSUMERS) {
     // ------------------------------ producer: one box per stage ------------------------------
-    const uint64_t pol = policy_evict_first();
+    const bool im2col = second && g.conv;
+    const uint64_t pol = im2col ? policy_evict_normal() : policy_evict_first();   // taps re-read X
+    const int tap = im2col ? cb / g.cv_cpb : 0;
+    const int c0 = im2col ? (cb % g.cv_cpb) * rtc::COLS : cb * rtc::COLS;
+    const uint16_t off_w = (uint16_t)((tap % (im2col ? g.cv_S : 1)) * g.cv_dil_w);
+    const uint16_t off_h = (uint16_t)((tap / (im2col ? g.cv_S : 1)) * g.cv_dil_h);
     for (int it = 0; it < nstage; ++it) {
       const int s = it % rtc::NS;
       if (it >= rtc::NS) mbar_wait(&empty_bar[s], ((it / rtc::NS) - 1) & 1, 40);
       if (elect_one()) {
+        const long long m0 = m_begin + (long long)it * rtc::TOK;
         mbar_arrive_expect_tx(&full_bar[s], rtc::STAGE_BYTES);
-        tma_load_2d(smem + s * rtc::STAGE_BYTES, tm, &full_bar[s], cb * rtc::COLS,
-                    (int)(m_begin + (long long)it * rtc::TOK), pol);
+        if (im2col) {
+          const int hw = g.cv_Ho * g.cv_Wo;
+          const int n = (int)(m0 / hw);
+          const int rem = (int)(m0 - (long long)n * hw);
+          tma_load_im2col(smem + s * rtc::STAGE_BYTES, tm, &full_bar[s], c0,
+                          (rem % g.cv_Wo) * g.cv_str_w - g.cv_pad_w,
+                          (rem / g.cv_Wo) * g.cv_str_h - g.cv_pad_h, n, off_w, off_h, pol);
+        } else {
+          tma_load_2d(smem + s * rtc::STAGE_BYTES, tm, &full_bar[s], c0, (int)m0, pol);
+        }
       }
       __syncwarp();
     }
@@ -349,13 +344,18 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
   named_bar_sync(1, rtc::CONSUMERS * 32);
   for (int idx = threadIdx.x; idx < rtc::COLS * JW; idx += rtc::CONSUMERS * 32) {
     const int c = idx / JW, j = idx % JW;
-    const int gc = cb * rtc::COLS + c;
+    int gc = cb * rtc::COLS + c;
+    long long tap_off = 0;
+    if (second && g.conv) {            // column block = (tap, 64-channel block); dA is OIHW
+      gc = (cb % g.cv_cpb) * rtc::COLS + c;
+      tap_off = cb / g.cv_cpb;
+    }
     if (gc >= p.C || j >= g.r) continue;
     float sum = 0.f;
 #pragma unroll
     for (int w = 0; w < rtc::CONSUMERS; ++w) sum += red[(w * rtc::COLS + c) * JW + j];
     if (p.partial != nullptr) p.partial[((long long)sp * p.C + gc) * g.rp + j] = sum;
-    else atomicAdd(p.out + gc * p.out_cs + j * p.out_js, sum * g.scale);
+    else atomicAdd(p.out + tap_off + gc * p.out_cs + j * p.out_js, sum * g.scale);
   }
 }
 
@@ -466,6 +466,53 @@ static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* t
   }
   return e;
 }
+
+// dA of a LoRA convolution: dA[j, c, kh, kw] += s * sum_m dT[m, j] * X[pixel(m) + tap, c], with the
+// im2col view of X streamed by TMA (tmX: the forward's im2col map).  geo = {N,H,W,C,Ho,Wo,R,S,
+// str_h,str_w,pad_h,pad_w,dil_h,dil_w}; dA is OIHW fp32 (accumulated with atomics).
+template <typename T>
+cudaError_t launch_conv_grad_a_tc(const CUtensorMap* tmX, const void* dT, float scale, float* dA,
+                                  const int* geo, int r, int sms, cudaStream_t stream) {
+  const int N = geo[0], C = geo[3], Ho = geo[4], Wo = geo[5], R = geo[6], S = geo[7];
+  const long long M = (long long)N * Ho * Wo;
+  RedProblem pa = {}, pb = {};
+  RedTcGeom g = {};
+  g.M = M; g.r = r; g.scale = scale; g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  g.conv = 1; g.cv_S = S; g.cv_cpb = (C + rtc::COLS - 1) / rtc::COLS; g.cv_C = C; g.cv_Ho = Ho; g.cv_Wo = Wo;
+  g.cv_str_h = geo[8]; g.cv_str_w = geo[9]; g.cv_pad_h = geo[10]; g.cv_pad_w = geo[11];
+  g.cv_dil_h = geo[12]; g.cv_dil_w = geo[13];
+  const int col_blocks = R * S * g.cv_cpb;
+  g.rows_per_block = tc_rows_per_block(M, col_blocks * rtc::COLS, 0, sms);
+  const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
+  pa.P = dT; pa.out = dA; pa.out_cs = (long long)R * S; pa.out_js = (long long)C * R * S; pa.partial = nullptr;
+  pa.C = C; pa.col_blocks = col_blocks; pa.splits = splits; pa.rows_per_block = g.rows_per_block;
+  g.blocks0 = 0;   // every block works on problem 1
+  const int nblk = col_blocks * splits;
+  cudaError_t e = cudaSuccess;
+#define LAUNCH_CV(NJ_)                                                                           \
+  do {                                                                                           \
+    auto kern = lora_grad_mma_kernel<T, NJ_>;                                                    \
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, rtc::SMEM_BYTES);    \
+    cudaLaunchConfig_t cfg = {};                                                                 \
+    cudaLaunchAttribute attr[1];                                                                 \
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                             \
+    attr[0].val.programmaticStreamSerializationAllowed = 1;                                      \
+    cfg.gridDim = dim3(nblk, 1, 1);                                                              \
+    cfg.blockDim = dim3(rtc::NT, 1, 1);                                                          \
+    cfg.dynamicSmemBytes = rtc::SMEM_BYTES;                                                      \
+    cfg.stream = stream;                                                                         \
+    cfg.attrs = attr;                                                                            \
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;                                                        \
+    e = cudaLaunchKernelEx(&cfg, kern, *tmX, *tmX, pb, pa, g);                                   \
+  } while (0)
+  if (r <= 8) LAUNCH_CV(1); else LAUNCH_CV(2);
+#undef LAUNCH_CV
+  return e;
+}
+template cudaError_t launch_conv_grad_a_tc<__nv_bfloat16>(const CUtensorMap*, const void*, float, float*,
+                                                          const int*, int, int, cudaStream_t);
+template cudaError_t launch_conv_grad_a_tc<__half>(const CUtensorMap*, const void*, float, float*, const int*,
+                                                   int, int, cudaStream_t);
 
 // Both gradient reductions in one launch.  dB <- (dY, T), dA <- (X, dT); either may be skipped.
 // tmDY / tmX: [M,N] / [M,K] tensor maps with a [128 x 64] box (16-bit io); null selects the SIMT

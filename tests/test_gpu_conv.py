@@ -118,3 +118,21 @@ def test_extended_injection_runs_a_resnet_block():
     y_ref.mean().backward()
     for a, b_ in zip(ours, layers):
         assert rel_err(a.lora_up.weight.grad, b_.lora_up.weight.grad) < 5e-2
+
+
+def test_first_cuda_call_of_the_autograd_thread_is_ours():
+    """Fresh process: the backward thread's very first CUDA work is our zcat launch (tensor-map
+    encoding is a driver call and needs the context bound on that thread)."""
+    import subprocess
+    import sys
+    code = (
+        "import torch, diffusion_finetuning_b200 as L\n"
+        "m = L.LoraInjectedConv2d(128, 128, 3, padding=1, r=4).cuda().to(torch.bfloat16)\n"
+        "m.conv.requires_grad_(False)\n"
+        "x = torch.randn(2, 128, 8, 8, device='cuda', dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)\n"
+        "dy = torch.randn(2, 128, 8, 8, device='cuda', dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)\n"
+        "m(x).backward(dy); torch.cuda.synchronize(); print('ok', float(x.grad.float().abs().sum()) > 0)\n")
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok True" in out.stdout, out.stderr[-2000:]
