@@ -167,7 +167,7 @@ class Trainer:
     optimizer over the returned parameter generators -> fwd/bwd/clip/step
     (train_lora_dreambooth.py:595-676, 816-888)."""
 
-    def __init__(self, device, rank_r, autocast=True, channels_last=False):
+    def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True):
         import itertools
         import diffusion_finetuning_b200 as L
         from diffusion_finetuning_b200 import dp
@@ -185,6 +185,7 @@ class Trainer:
             for m in self.unet.modules():
                 if isinstance(m, L.LoraInjectedLinear):
                     m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
+        self.groups = L.fuse_sibling_projections(self.unet) if fuse else []
         self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
         self.arena.broadcast_params(0)
         self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True)
@@ -291,6 +292,7 @@ def config_dict(args, batch):
             "lora": f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out", "latents": f"{args.res}x{args.res}",
             "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
             "optimizer": "AdamW lr 1e-4, clip 1.0", "memory_format": getattr(args, "memory_format", "nchw"),
+            "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch",
             "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
 
 
@@ -304,6 +306,8 @@ def main():
     ap.add_argument("--res", type=int, default=64)
     ap.add_argument("--rank", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fuse", action="store_true",
+                    help="run q/k/v LoRA layers one launch each instead of fused per attention block")
     ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
                     help="memory format of the frozen stock-PyTorch UNet (the reference scripts use nchw)")
     ap.add_argument("--breakdown", default=None, help="write the per-kernel breakdown JSON here")
@@ -332,7 +336,7 @@ def main():
     from diffusion_finetuning_b200 import ops
     nat.lib()
 
-    tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last")
+    tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last", fuse=not args.no_fuse)
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
     for i in range(args.warmup):

@@ -32,7 +32,8 @@ cudaError_t launch_tc(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&
 int tc2_smem_bytes(int BN, int* stages_out);
 template <typename TIO>
 cudaError_t launch_tc2(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                       const CUtensorMap&, const CUtensorMap&, const TcParams&, int, cudaStream_t);
+                       const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                       const TcParams&, int, cudaStream_t);
 cudaError_t launch_conv_repack(const void*, int, void*, int, int, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_conv_pack(const void*, const void*, int, const void*, int, void*, void*, void*, int,
                              int, int, int, int, int, int, int, int, cudaStream_t);
@@ -56,6 +57,10 @@ int grad_reduce_splits(long long M, int C, int C_other, int esize, int sms);
 template <typename T>
 cudaError_t launch_conv_grad_a_tc(const CUtensorMap*, const void*, float, float*, const int*, int, int,
                                   cudaStream_t);
+template <typename T>
+cudaError_t launch_grads_fused_tc(const CUtensorMap* const*, const CUtensorMap*, const void*, const void*,
+                                  const float*, float* const*, float* const*, long long, int, int, int,
+                                  const int*, int, cudaStream_t);
 template <typename TW, typename TL, int MODE>
 cudaError_t launch_merge(const void*, void*, const void*, const void*, float, int, int, int,
                          float*, cudaStream_t);
@@ -282,13 +287,16 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
 
 // CTA-pair variant (linear_tc2.cu): same math, tcgen05 cta_group::2, 256-row blocks per pair
 struct ConvGeoH { int N, H, W, C, Ho, Wo, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w; };
+// X given as `n` tensors [M, cols] side by side along K (cols % 64 == 0, n <= 3)
+struct XSegs { int n; int cols; const void* ptr[3]; long long ld[3]; };
 
 static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, bool has_bias,
                    const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
                    void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
-                   cudaStream_t stream, const ConvGeoH* cg = nullptr) {
+                   cudaStream_t stream, const ConvGeoH* cg = nullptr, const XSegs* xs = nullptr) {
   TcParams p;
   memset(&p, 0, sizeof(p));
+  if (xs) p.kseg = xs->cols / 64;
   if (cg) {
     p.conv = 1; p.cv_S = cg->S; p.cv_cpb = (cg->C + 63) / 64; p.cv_Ho = cg->Ho; p.cv_Wo = cg->Wo;
     p.cv_pad_h = cg->pad_h; p.cv_pad_w = cg->pad_w; p.cv_str_h = cg->str_h; p.cv_str_w = cg->str_w;
@@ -315,13 +323,20 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   p.idesc_tail = p.idesc_main;
   const int H = (p.BN + 16) / 2;
 
-  CUtensorMap tmX, tmWa, tmWb, tmS1, tmS2, tmY;
+  CUtensorMap tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY;
   int rc;
   if (cg) {
     if ((rc = get_tmap_im2col(&tmX, X, cg->N, cg->H, cg->W, cg->C, cg->R, cg->S, cg->str_h, cg->str_w,
                               cg->pad_h, cg->pad_w, cg->dil_h, cg->dil_w, io_dtype))) return rc;
+  } else if (xs) {
+    CUtensorMap* dst[3] = {&tmX, &tmX1, &tmX2};
+    for (int i = 0; i < xs->n; ++i)
+      if ((rc = get_tmap(dst[i], xs->ptr[i], (uint64_t)M, (uint64_t)xs->cols, (uint64_t)xs->ld[i], 128, 64,
+                         io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    for (int i = xs->n; i < 3; ++i) *dst[i] = tmX;
   } else if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
                             CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  if (!xs) { tmX1 = tmX; tmX2 = tmX; }
   if ((rc = get_tmap(&tmWa, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)(H - 16), 64,
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmWb, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)H, 64, io_dtype,
@@ -333,8 +348,8 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   cudaError_t e = io_dtype == B200LORA_BF16
-                      ? launch_tc2<__nv_bfloat16>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream)
-                      : launch_tc2<__half>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream);
+                      ? launch_tc2<__nv_bfloat16>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream)
+                      : launch_tc2<__half>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream);
   if (e != cudaSuccess) {
     if (!g_err[0]) set_error("tc2 launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
@@ -492,6 +507,79 @@ extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layou
   const void* s2p = pk ? pk + 2ll * (16 * ((int64_t)K + N) + 64ll * N) : nullptr;
   return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, s1p, A, 1, K, ab_dtype,
                             s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+}
+
+// =========================================================================================
+// Fused sibling projections: layers that read the SAME input (attention to_q/to_k/to_v)
+// run as one GEMM over the concatenated outputs.  Forward is b200lora_lora_gemm on the concatenated
+// operands (W_cat [nseg*Nseg, K], pack of A_cat [r_total, K] and the block-diagonal, scale-folded B);
+// these two entry points are the backward: dY arrives as nseg separate tensors.
+// =========================================================================================
+extern "C" int b200lora_linear_bwd_dx_fused(const void* const* dY, const int64_t* ld_dy, int nseg,
+                                            const void* Wt, const void* pack, void* dX, void* dT_out,
+                                            int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                                            b200lora_stream_t stream_) {
+  // dX = sum_i dY_i·W0_i + dT·A_cat with dT = [dY_0 | dY_1 | ..]·B_bd riding as rank rows; Wt is
+  // W_catᵀ stored [K, nseg*Nseg] (the W_NK operand of the transposed problem)
+  g_err[0] = 0;
+  if (!dY || !ld_dy || !Wt || !pack || !dX) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (nseg < 1 || nseg > 3) { set_error("fused backward takes 1..3 segments (got %d)", nseg); return B200LORA_E_SHAPE; }
+  if (Nseg % 64) { set_error("fused backward needs segment width %% 64 == 0 (got %d)", Nseg); return B200LORA_E_SHAPE; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("fused path is 16-bit io only"); return B200LORA_E_DTYPE; }
+  if (M <= 0) return 0;
+  const int Ncat = nseg * Nseg;
+  XSegs xs;
+  xs.n = nseg; xs.cols = Nseg;
+  for (int i = 0; i < nseg; ++i) {
+    if (!dY[i] || !aligned16(dY[i]) || (ld_dy[i] % 8)) { set_error("fused backward: dY[%d] null or misaligned", i); return B200LORA_E_ALIGN; }
+    xs.ptr[i] = dY[i]; xs.ld[i] = ld_dy[i];
+  }
+  if (!tc_applicable(dY[0], ld_dy[0], Wt, Ncat, B200LORA_W_NK, dX, K, r_total, io_dtype, K)) return B200LORA_E_ALIGN;
+  const char* pk = reinterpret_cast<const char*>(pack);
+  const void* s1p = pk + 2ll * 16 * K;                                       // Bt_pack [16, Ncat]
+  const void* s2p = pk + 2ll * (16 * ((int64_t)K + Ncat) + 64ll * Ncat);     // At_pack [K, 64]
+  return run_tc2(dY[0], ld_dy[0], Wt, Ncat, false, s1p, s2p, 1.0f, dX, K, dT_out, M, Ncat, K, r_total, io_dtype,
+                 reinterpret_cast<cudaStream_t>(stream_), nullptr, &xs);
+}
+
+extern "C" int b200lora_lora_grads_fused(const void* const* dY, const int64_t* ld_dy, int nseg, const void* X,
+                                         const void* T, const void* dT, const float* scales,
+                                         float* const* dA, float* const* dB, int64_t M, int K, int Nseg,
+                                         const int* r_each, int io_dtype, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!dY || !ld_dy || !X || !T || !dT || !scales || !dA || !dB || !r_each) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (nseg < 1 || nseg > 3) { set_error("fused grads take 1..3 segments (got %d)", nseg); return B200LORA_E_SHAPE; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("fused path is 16-bit io only"); return B200LORA_E_DTYPE; }
+  if ((K % 8) || (Nseg % 8)) { set_error("fused grads need K and N multiples of 8"); return B200LORA_E_ALIGN; }
+  int r_total = 0;
+  for (int i = 0; i < nseg; ++i) {
+    if (r_each[i] < 1 || !dA[i] || !dB[i] || !dY[i]) { set_error("fused grads: bad segment %d", i); return B200LORA_E_ARG; }
+    r_total += r_each[i];
+  }
+  if (r_total > 16) { set_error("fused grads need sum of ranks <= 16 (got %d)", r_total); return B200LORA_E_SHAPE; }
+  if (M <= 0) return 0;
+  DevInfo di = dev_info();
+  if (!di.ok || di.major != 10) { set_error("fused grads need an sm_100 device"); return B200LORA_E_CUDA; }
+  CUtensorMap tmDY[3], tmX;
+  const CUtensorMap* pDY[3];
+  int rc;
+  for (int i = 0; i < nseg; ++i) {
+    if (!aligned16(dY[i]) || (ld_dy[i] % 8)) { set_error("fused grads: dY[%d] misaligned", i); return B200LORA_E_ALIGN; }
+    if ((rc = get_tmap(&tmDY[i], dY[i], (uint64_t)M, (uint64_t)Nseg, (uint64_t)ld_dy[i], 128, 64, io_dtype,
+                       CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    pDY[i] = &tmDY[i];
+  }
+  if (!aligned16(X)) { set_error("fused grads: X misaligned"); return B200LORA_E_ALIGN; }
+  if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)K, (uint64_t)K, 128, 64, io_dtype,
+                     CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  cudaError_t e = io_dtype == B200LORA_BF16
+                      ? launch_grads_fused_tc<__nv_bfloat16>(pDY, &tmX, T, dT, scales, dA, dB, M, K, Nseg, nseg,
+                                                             r_each, di.sms, stream)
+                      : launch_grads_fused_tc<__half>(pDY, &tmX, T, dT, scales, dA, dB, M, K, Nseg, nseg, r_each,
+                                                      di.sms, stream);
+  if (e != cudaSuccess) { set_error("fused grads launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
 }
 
 // =========================================================================================

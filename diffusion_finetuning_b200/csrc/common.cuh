@@ -50,6 +50,7 @@ struct TcParams {
   // block); rows are output pixels in (n, oh, ow) order
   int conv, cv_S, cv_cpb, cv_Ho, cv_Wo;
   int cv_pad_h, cv_pad_w, cv_str_h, cv_str_w, cv_dil_h, cv_dil_w;
+  int kseg;                   // != 0: X is split along K into tensors of kseg k-blocks each (<= 3)
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;
 };

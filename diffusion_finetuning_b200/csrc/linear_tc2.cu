@@ -84,7 +84,8 @@ struct Sched2 {
 
 template <typename TIO, bool DBG>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc2::NUM_THREADS, 1)
-lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmWa,
+lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmX1,
+                     const __grid_constant__ CUtensorMap tmX2, const __grid_constant__ CUtensorMap tmWa,
                      const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmS1,
                      const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmY,
                      const TcParams p) {
@@ -200,8 +201,13 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                 tma_load_im2col_2sm(a_dst, &tmX, full0, cb * BK, cv_w, cv_h, cv_n,
                                     (uint16_t)((tap % p.cv_S) * p.cv_dil_w),
                                     (uint16_t)((tap / p.cv_S) * p.cv_dil_h), pol_x);
-              else
+              else if (p.kseg == 0)
                 tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
+              else {   // X split along K into equal segments, one tensor each (fused sibling backward)
+                const int sg = kb / p.kseg;
+                const CUtensorMap* xm = sg == 0 ? &tmX : (sg == 1 ? &tmX1 : &tmX2);
+                tma_load_2d_2sm(a_dst, xm, full0, (kb - sg * p.kseg) * BK, m_blk * 256 + (int)rank * BM, pol_x);
+              }
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
               tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);                  // H rows
@@ -506,7 +512,8 @@ bool pdl_enabled() {
 }
 
 template <typename TIO, bool DBG>
-static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmWa,
+static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CUtensorMap& tmX2,
+                                   const CUtensorMap& tmWa,
                                    const CUtensorMap& tmWb, const CUtensorMap& tmS1,
                                    const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p,
                                    int smem_bytes, cudaStream_t stream) {
@@ -552,7 +559,7 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
   const int num_tiles = p.num_m_blk * p.num_n_blk;
   const int ncl = num_tiles < max_clusters ? num_tiles : max_clusters;
   cfg.gridDim = dim3(2 * ncl, 1, 1);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmX, tmWa, tmWb, tmS1, tmS2, tmY, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p);
   if (e != cudaSuccess)
     set_error("tc2: cudaLaunchKernelEx(grid=%d, smem=%d, BN=%d, stages=%d): %s", 2 * ncl, smem_bytes, p.BN,
               p.stages, cudaGetErrorString(e));
@@ -560,20 +567,22 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
 }
 
 template <typename TIO>
-cudaError_t launch_tc2(const CUtensorMap& tmX, const CUtensorMap& tmWa, const CUtensorMap& tmWb,
-                       const CUtensorMap& tmS1, const CUtensorMap& tmS2, const CUtensorMap& tmY,
-                       const TcParams& p, int smem_bytes, cudaStream_t stream) {
+cudaError_t launch_tc2(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CUtensorMap& tmX2,
+                       const CUtensorMap& tmWa, const CUtensorMap& tmWb, const CUtensorMap& tmS1,
+                       const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p, int smem_bytes,
+                       cudaStream_t stream) {
   if (p.dbg != nullptr)
-    return launch_tc2_impl<TIO, true>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
-  return launch_tc2_impl<TIO, false>(tmX, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
+    return launch_tc2_impl<TIO, true>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
+  return launch_tc2_impl<TIO, false>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
 }
 
-template cudaError_t launch_tc2<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&,
-                                               const CUtensorMap&, const CUtensorMap&,
-                                               const CUtensorMap&, const CUtensorMap&,
-                                               const TcParams&, int, cudaStream_t);
+template cudaError_t launch_tc2<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                               const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                               const CUtensorMap&, const CUtensorMap&, const TcParams&, int,
+                                               cudaStream_t);
 template cudaError_t launch_tc2<__half>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                                         const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                                        const TcParams&, int, cudaStream_t);
+                                        const CUtensorMap&, const CUtensorMap&, const TcParams&, int,
+                                        cudaStream_t);
 
 }  // namespace b200

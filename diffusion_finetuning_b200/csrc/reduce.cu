@@ -191,50 +191,71 @@ constexpr int CTAS_PER_SM = 3;
 }
 
 // B fragment of P[tok0 .. tok0+16, 8*jh .. 8*jh+8): lane (g = lane/4, t = lane%4) holds
-// (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero
+// (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero.
+// `P` points at the problem's first rank column, `ldp` is the row stride in elements.
 __device__ __forceinline__ void load_p_frag(const unsigned short* __restrict__ P, long long tok0,
-                                            int j, int r, long long M, int t, uint32_t (&b)[2]) {
+                                            int j, int r, int ldp, long long M, int t, uint32_t (&b)[2]) {
   b[0] = 0u; b[1] = 0u;
   if (j < r) {
     const long long k0 = tok0 + 2 * t;
     if (k0 + 9 < M) {
-      const unsigned short* q = P + k0 * r + j;
-      b[0] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + r) << 16);
-      b[1] = (uint32_t)__ldg(q + 8 * r) | ((uint32_t)__ldg(q + 9 * r) << 16);
+      const unsigned short* q = P + k0 * ldp + j;
+      b[0] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + ldp) << 16);
+      b[1] = (uint32_t)__ldg(q + 8 * ldp) | ((uint32_t)__ldg(q + 9 * ldp) << 16);
     } else {
       uint32_t e[4];
       const int off[4] = {0, 1, 8, 9};
 #pragma unroll
-      for (int i = 0; i < 4; ++i) e[i] = (k0 + off[i] < M) ? (uint32_t)__ldg(P + (k0 + off[i]) * r + j) : 0u;
+      for (int i = 0; i < 4; ++i) e[i] = (k0 + off[i] < M) ? (uint32_t)__ldg(P + (k0 + off[i]) * ldp + j) : 0u;
       b[0] = e[0] | (e[1] << 16);
       b[1] = e[2] | (e[3] << 16);
     }
   }
 }
 
+// One reduction problem of a launch: G[c, j] = scale * sum_m Z[m, c] * P[m, j0 + j], j < r.
+// Ranks [r_off[d], r_off[d+1]) go to out[d] (several destinations = the dA rows of fused siblings).
+struct RedTcProb {
+  const void* P;
+  int ldp, j0, r;
+  float scale;
+  float* out[3];
+  int r_off[4];
+  long long out_cs, out_js;
+  float* partial;          // deterministic mode: [splits, C, rp] workspace instead of atomics
+  int C, col_blocks, block_start;
+};
+struct RedTcGroup {
+  int n;
+  RedTcProb p[4];
+};
+
 struct RedTcGeom {
   long long M;
   int rows_per_block;   // multiple of rtc::TOK
-  int blocks0, r, rp;   // rp: rank stride of the deterministic workspace (4 / 8 / 16)
-  float scale;
-  // problem 1 as a convolution's dA: Z = im2col(X) [M, taps * cpb * 64], never materialised
+  int rp;               // rank stride of the deterministic workspace (4 / 8 / 16)
+  // problem 0 as a convolution's dA: Z = im2col(X) [M, taps * cpb * 64], never materialised
   int conv, cv_S, cv_cpb, cv_C, cv_Ho, cv_Wo, cv_pad_h, cv_pad_w, cv_str_h, cv_str_w, cv_dil_h, cv_dil_w;
 };
 
 template <typename T, int NJ>
 __global__ void __launch_bounds__(rtc::NT)
 lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
-                     const RedProblem p0, const RedProblem p1, const RedTcGeom g) {
+                     const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3,
+                     const __grid_constant__ RedTcGroup grp, const RedTcGeom g) {
   extern __shared__ uint8_t red_smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[rtc::NS];
   __shared__ __align__(8) uint64_t empty_bar[rtc::NS];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(red_smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
 
-  const bool second = (int)blockIdx.x >= g.blocks0;
-  const RedProblem& p = second ? p1 : p0;
-  const CUtensorMap* tm = second ? &tm1 : &tm0;
-  const int bid = second ? blockIdx.x - g.blocks0 : blockIdx.x;
+  int pid = 0;
+#pragma unroll
+  for (int i = 1; i < 4; ++i)
+    if (i < grp.n && (int)blockIdx.x >= grp.p[i].block_start) pid = i;
+  const RedTcProb& p = grp.p[pid];
+  const CUtensorMap* tm = pid == 0 ? &tm0 : (pid == 1 ? &tm1 : (pid == 2 ? &tm2 : &tm3));
+  const int bid = blockIdx.x - p.block_start;
   const int cb = bid % p.col_blocks;
   const int sp = bid / p.col_blocks;
   const long long m_begin = (long long)sp * g.rows_per_block;
@@ -255,7 +276,7 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
 
   if (warp == rtc::CONSUMERS) {
     // ------------------------------ producer: one box per stage ------------------------------
-    const bool im2col = second && g.conv;
+    const bool im2col = pid == 0 && g.conv;
     const uint64_t pol = im2col ? policy_evict_normal() : policy_evict_first();   // taps re-read X
     const int tap = im2col ? cb / g.cv_cpb : 0;
     const int c0 = im2col ? (cb % g.cv_cpb) * rtc::COLS : cb * rtc::COLS;
@@ -285,7 +306,7 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
 
   // ------------------------------ consumers: 16 tokens per warp ------------------------------
   const int gq = lane >> 2, tq = lane & 3;
-  const unsigned short* __restrict__ P = reinterpret_cast<const unsigned short*>(p.P);
+  const unsigned short* __restrict__ P = reinterpret_cast<const unsigned short*>(p.P) + p.j0;
   float acc[4][NJ][4];
 #pragma unroll
   for (int ct = 0; ct < 4; ++ct)
@@ -301,7 +322,7 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
 
   uint32_t bnext[NJ][2];
 #pragma unroll
-  for (int jh = 0; jh < NJ; ++jh) load_p_frag(P, m_begin + warp * 16, gq + 8 * jh, g.r, g.M, tq, bnext[jh]);
+  for (int jh = 0; jh < NJ; ++jh) load_p_frag(P, m_begin + warp * 16, gq + 8 * jh, p.r, p.ldp, g.M, tq, bnext[jh]);
 
   for (int it = 0; it < nstage; ++it) {
     const int s = it % rtc::NS;
@@ -311,7 +332,8 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
     if (it + 1 < nstage) {
 #pragma unroll
       for (int jh = 0; jh < NJ; ++jh)
-        load_p_frag(P, m_begin + (long long)(it + 1) * rtc::TOK + warp * 16, gq + 8 * jh, g.r, g.M, tq, bnext[jh]);
+        load_p_frag(P, m_begin + (long long)(it + 1) * rtc::TOK + warp * 16, gq + 8 * jh, p.r, p.ldp, g.M, tq,
+                    bnext[jh]);
     }
     mbar_wait(&full_bar[s], (it / rtc::NS) & 1, 41);
     const uint32_t st_addr = smem_base + s * rtc::STAGE_BYTES + row_off;
@@ -346,16 +368,20 @@ lora_grad_mma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_const
     const int c = idx / JW, j = idx % JW;
     int gc = cb * rtc::COLS + c;
     long long tap_off = 0;
-    if (second && g.conv) {            // column block = (tap, 64-channel block); dA is OIHW
+    if (pid == 0 && g.conv) {          // column block = (tap, 64-channel block); dA is OIHW
       gc = (cb % g.cv_cpb) * rtc::COLS + c;
       tap_off = cb / g.cv_cpb;
     }
-    if (gc >= p.C || j >= g.r) continue;
+    if (gc >= p.C || j >= p.r) continue;
     float sum = 0.f;
 #pragma unroll
     for (int w = 0; w < rtc::CONSUMERS; ++w) sum += red[(w * rtc::COLS + c) * JW + j];
-    if (p.partial != nullptr) p.partial[((long long)sp * p.C + gc) * g.rp + j] = sum;
-    else atomicAdd(p.out + tap_off + gc * p.out_cs + j * p.out_js, sum * g.scale);
+    if (p.partial != nullptr) {
+      p.partial[((long long)sp * p.C + gc) * g.rp + j] = sum;
+    } else {
+      const int d = (j >= p.r_off[1]) + (j >= p.r_off[2]);
+      atomicAdd(p.out[d] + tap_off + gc * p.out_cs + (j - p.r_off[d]) * p.out_js, sum * p.scale);
+    }
   }
 }
 
@@ -404,31 +430,14 @@ static void fill_problem(RedProblem& p, const void* Z, long long ldz, const void
   p.splits = (int)((M + rpb - 1) / rpb);
 }
 
+// launch helper shared by the three entry points below
 template <typename T>
-static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* tmX, const void* Tm,
-                                   const void* dT, float scale, float* dA, float* dB, float* partA,
-                                   float* partB, long long M, int K, int N, int r, int sms,
-                                   cudaStream_t stream) {
-  RedProblem pb = {}, pa = {};
-  RedTcGeom g = {};
-  g.M = M; g.r = r; g.scale = scale;
-  g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
-  g.rows_per_block = tc_rows_per_block(M, dB ? N : 0, dA ? K : 0, sms);
-  const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
-  int nb = 0, na = 0;
-  if (dB) {
-    pb.P = Tm; pb.out = dB; pb.out_cs = r; pb.out_js = 1; pb.partial = partB; pb.C = N;
-    pb.col_blocks = (N + rtc::COLS - 1) / rtc::COLS; pb.splits = splits; pb.rows_per_block = g.rows_per_block;
-    nb = pb.col_blocks * splits;
-  }
-  if (dA) {
-    pa.P = dT; pa.out = dA; pa.out_cs = 1; pa.out_js = K; pa.partial = partA; pa.C = K;
-    pa.col_blocks = (K + rtc::COLS - 1) / rtc::COLS; pa.splits = splits; pa.rows_per_block = g.rows_per_block;
-    na = pa.col_blocks * splits;
-  }
-  g.blocks0 = nb;
-  const CUtensorMap& m0 = dB ? *tmDY : *tmX;   // an absent problem never dereferences its map
-  const CUtensorMap& m1 = dA ? *tmX : *tmDY;
+static cudaError_t launch_mma_group(const CUtensorMap* const* tms, const RedTcGroup& grp, const RedTcGeom& g,
+                                    int nblocks, int max_r, cudaStream_t stream) {
+  const CUtensorMap& m0 = *tms[0];
+  const CUtensorMap& m1 = *tms[grp.n > 1 ? 1 : 0];
+  const CUtensorMap& m2 = *tms[grp.n > 2 ? 2 : 0];
+  const CUtensorMap& m3 = *tms[grp.n > 3 ? 3 : 0];
   cudaError_t e = cudaSuccess;
 #define LAUNCH_TC(NJ_)                                                                           \
   do {                                                                                           \
@@ -443,18 +452,57 @@ static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* t
     cudaLaunchAttribute attr[1];                                                                 \
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                             \
     attr[0].val.programmaticStreamSerializationAllowed = 1;                                      \
-    cfg.gridDim = dim3(nb + na, 1, 1);                                                           \
+    cfg.gridDim = dim3(nblocks, 1, 1);                                                           \
     cfg.blockDim = dim3(rtc::NT, 1, 1);                                                          \
     cfg.dynamicSmemBytes = rtc::SMEM_BYTES;                                                      \
     cfg.stream = stream;                                                                         \
     cfg.attrs = attr;                                                                            \
     cfg.numAttrs = pdl_enabled() ? 1 : 0;                                                        \
-    e = cudaLaunchKernelEx(&cfg, kern, m0, m1, pb, pa, g);                                       \
-    if (e != cudaSuccess) return e;                                                              \
+    e = cudaLaunchKernelEx(&cfg, kern, m0, m1, m2, m3, grp, g);                                  \
   } while (0)
-  if (r <= 8) LAUNCH_TC(1); else LAUNCH_TC(2);
+  if (max_r <= 8) LAUNCH_TC(1); else LAUNCH_TC(2);
 #undef LAUNCH_TC
-  e = cudaGetLastError();
+  return e;
+}
+
+static void fill_tc_prob(RedTcProb& q, const void* P, int ldp, int j0, int r, float scale, float* out,
+                         long long out_cs, long long out_js, float* partial, int C) {
+  q.P = P; q.ldp = ldp; q.j0 = j0; q.r = r; q.scale = scale;
+  q.out[0] = q.out[1] = q.out[2] = out;
+  q.r_off[0] = 0; q.r_off[1] = q.r_off[2] = q.r_off[3] = r;
+  q.out_cs = out_cs; q.out_js = out_js; q.partial = partial; q.C = C;
+  q.col_blocks = (C + rtc::COLS - 1) / rtc::COLS;
+}
+
+template <typename T>
+static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* tmX, const void* Tm,
+                                   const void* dT, float scale, float* dA, float* dB, float* partA,
+                                   float* partB, long long M, int K, int N, int r, int sms,
+                                   cudaStream_t stream) {
+  RedProblem pb = {}, pa = {};   // for the finalize kernel of the deterministic mode
+  RedTcGroup grp = {};
+  RedTcGeom g = {};
+  g.M = M;
+  g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  g.rows_per_block = tc_rows_per_block(M, dB ? N : 0, dA ? K : 0, sms);
+  const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
+  const CUtensorMap* tms[4] = {tmDY, tmX, tmDY, tmDY};
+  int nblk = 0;
+  if (dB) {
+    RedTcProb& q = grp.p[grp.n];
+    fill_tc_prob(q, Tm, r, 0, r, scale, dB, r, 1, partB, N);
+    q.block_start = nblk; nblk += q.col_blocks * splits;
+    tms[grp.n++] = tmDY;
+    pb.out = dB; pb.out_cs = r; pb.out_js = 1; pb.partial = partB; pb.C = N; pb.splits = splits;
+  }
+  if (dA) {
+    RedTcProb& q = grp.p[grp.n];
+    fill_tc_prob(q, dT, r, 0, r, scale, dA, 1, K, partA, K);
+    q.block_start = nblk; nblk += q.col_blocks * splits;
+    tms[grp.n++] = tmX;
+    pa.out = dA; pa.out_cs = 1; pa.out_js = K; pa.partial = partA; pa.C = K; pa.splits = splits;
+  }
+  cudaError_t e = launch_mma_group<T>(tms, grp, g, nblk, r, stream);
   if (e != cudaSuccess) return e;
   if ((partA && dA) || (partB && dB)) {
     const int n0 = dB ? N * g.rp : 0, n1 = dA ? K * g.rp : 0;
@@ -467,6 +515,54 @@ static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* t
   return e;
 }
 
+// Fused sibling layers (same input X, outputs side by side): nseg problems dB_i <- (dY_i, T[:, off_i ..])
+// and one problem dA_cat <- (X, dT) whose rank rows land in nseg destinations.  T / dT are [M, r_total].
+template <typename T>
+cudaError_t launch_grads_fused_tc(const CUtensorMap* const* tmDY, const CUtensorMap* tmX, const void* Tm,
+                                  const void* dT, const float* scales, float* const* dA, float* const* dB,
+                                  long long M, int K, int Nseg, int nseg, const int* r_each, int sms,
+                                  cudaStream_t stream) {
+  RedTcGroup grp = {};
+  RedTcGeom g = {};
+  g.M = M;
+  int r_total = 0, r_max = 0;
+  for (int i = 0; i < nseg; ++i) { r_total += r_each[i]; if (r_each[i] > r_max) r_max = r_each[i]; }
+  g.rp = 16;
+  g.rows_per_block = tc_rows_per_block(M, Nseg * nseg, K, sms);
+  const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
+  const CUtensorMap* tms[4] = {tmX, tmX, tmX, tmX};
+  int nblk = 0, off = 0;
+  for (int i = 0; i < nseg; ++i) {       // dB_i: scale s_i, ranks [off, off + r_i) of T
+    RedTcProb& q = grp.p[grp.n];
+    fill_tc_prob(q, Tm, r_total, off, r_each[i], scales[i], dB[i], r_each[i], 1, nullptr, Nseg);
+    q.block_start = nblk; nblk += q.col_blocks * splits;
+    tms[grp.n++] = tmDY[i];
+    off += r_each[i];
+  }
+  {                                      // dA_cat: dT already carries s_i (B was folded with it)
+    RedTcProb& q = grp.p[grp.n];
+    fill_tc_prob(q, dT, r_total, 0, r_total, 1.0f, dA[0], 1, K, nullptr, K);
+    int o = 0;
+    for (int i = 0; i < 3; ++i) {
+      q.out[i] = dA[i < nseg ? i : nseg - 1];
+      q.r_off[i] = o;
+      o += i < nseg ? r_each[i] : 0;
+    }
+    q.r_off[3] = r_total;
+    for (int i = nseg; i < 3; ++i) q.r_off[i] = r_total;
+    q.block_start = nblk; nblk += q.col_blocks * splits;
+    tms[grp.n++] = tmX;
+  }
+  return launch_mma_group<T>(tms, grp, g, nblk, r_total, stream);
+}
+template cudaError_t launch_grads_fused_tc<__nv_bfloat16>(const CUtensorMap* const*, const CUtensorMap*,
+                                                          const void*, const void*, const float*, float* const*,
+                                                          float* const*, long long, int, int, int, const int*,
+                                                          int, cudaStream_t);
+template cudaError_t launch_grads_fused_tc<__half>(const CUtensorMap* const*, const CUtensorMap*, const void*,
+                                                   const void*, const float*, float* const*, float* const*,
+                                                   long long, int, int, int, const int*, int, cudaStream_t);
+
 // dA of a LoRA convolution: dA[j, c, kh, kw] += s * sum_m dT[m, j] * X[pixel(m) + tap, c], with the
 // im2col view of X streamed by TMA (tmX: the forward's im2col map).  geo = {N,H,W,C,Ho,Wo,R,S,
 // str_h,str_w,pad_h,pad_w,dil_h,dil_w}; dA is OIHW fp32 (accumulated with atomics).
@@ -475,39 +571,22 @@ cudaError_t launch_conv_grad_a_tc(const CUtensorMap* tmX, const void* dT, float 
                                   const int* geo, int r, int sms, cudaStream_t stream) {
   const int N = geo[0], C = geo[3], Ho = geo[4], Wo = geo[5], R = geo[6], S = geo[7];
   const long long M = (long long)N * Ho * Wo;
-  RedProblem pa = {}, pb = {};
+  RedTcGroup grp = {};
   RedTcGeom g = {};
-  g.M = M; g.r = r; g.scale = scale; g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  g.M = M; g.rp = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
   g.conv = 1; g.cv_S = S; g.cv_cpb = (C + rtc::COLS - 1) / rtc::COLS; g.cv_C = C; g.cv_Ho = Ho; g.cv_Wo = Wo;
   g.cv_str_h = geo[8]; g.cv_str_w = geo[9]; g.cv_pad_h = geo[10]; g.cv_pad_w = geo[11];
   g.cv_dil_h = geo[12]; g.cv_dil_w = geo[13];
   const int col_blocks = R * S * g.cv_cpb;
   g.rows_per_block = tc_rows_per_block(M, col_blocks * rtc::COLS, 0, sms);
   const int splits = (int)((M + g.rows_per_block - 1) / g.rows_per_block);
-  pa.P = dT; pa.out = dA; pa.out_cs = (long long)R * S; pa.out_js = (long long)C * R * S; pa.partial = nullptr;
-  pa.C = C; pa.col_blocks = col_blocks; pa.splits = splits; pa.rows_per_block = g.rows_per_block;
-  g.blocks0 = 0;   // every block works on problem 1
-  const int nblk = col_blocks * splits;
-  cudaError_t e = cudaSuccess;
-#define LAUNCH_CV(NJ_)                                                                           \
-  do {                                                                                           \
-    auto kern = lora_grad_mma_kernel<T, NJ_>;                                                    \
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, rtc::SMEM_BYTES);    \
-    cudaLaunchConfig_t cfg = {};                                                                 \
-    cudaLaunchAttribute attr[1];                                                                 \
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                             \
-    attr[0].val.programmaticStreamSerializationAllowed = 1;                                      \
-    cfg.gridDim = dim3(nblk, 1, 1);                                                              \
-    cfg.blockDim = dim3(rtc::NT, 1, 1);                                                          \
-    cfg.dynamicSmemBytes = rtc::SMEM_BYTES;                                                      \
-    cfg.stream = stream;                                                                         \
-    cfg.attrs = attr;                                                                            \
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;                                                        \
-    e = cudaLaunchKernelEx(&cfg, kern, *tmX, *tmX, pb, pa, g);                                   \
-  } while (0)
-  if (r <= 8) LAUNCH_CV(1); else LAUNCH_CV(2);
-#undef LAUNCH_CV
-  return e;
+  RedTcProb& q = grp.p[0];
+  fill_tc_prob(q, dT, r, 0, r, scale, dA, (long long)R * S, (long long)C * R * S, nullptr, C);
+  q.col_blocks = col_blocks;
+  q.block_start = 0;
+  grp.n = 1;
+  const CUtensorMap* tms[4] = {tmX, tmX, tmX, tmX};
+  return launch_mma_group<T>(tms, grp, g, col_blocks * splits, r, stream);
 }
 template cudaError_t launch_conv_grad_a_tc<__nv_bfloat16>(const CUtensorMap*, const void*, float, float*,
                                                           const int*, int, int, cudaStream_t);

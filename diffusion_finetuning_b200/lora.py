@@ -68,6 +68,7 @@ class LoraInjectedLinear(nn.Module):
         nn.init.zeros_(self.lora_up.weight)                 # lora.py:47
         self._base_cache = ops.BaseWeightCache()
         self._grad_sink = None      # set by dp.LoraGradArena: dA/dB land in a flat fp32 arena
+        self._sibling_group = None  # set by fused.fuse_sibling_projections (opt-in q/k/v fusion)
 
     def _down_weight(self):
         """lora_down weight with a diagonal selector folded in (selector(T) = T·diag(d))."""
@@ -78,6 +79,11 @@ class LoraInjectedLinear(nn.Module):
         return sel.to(A.dtype) @ A
 
     def forward(self, input):
+        group = self._sibling_group
+        if group is not None:
+            y = group.member_forward(self, input)     # None: not fusable for this call
+            if y is not None:
+                return y
         A = self._down_weight()
         B = self.lora_up.weight
         if self.training and self.dropout.p > 0.0:

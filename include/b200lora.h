@@ -190,6 +190,31 @@ int b200lora_lora_grads(const void* dY, const void* X, const void* T, const void
 int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r);
 
 /*
+ * Fused sibling projections — layers that evaluate lora.py:49-50 on the SAME input (the to_q / to_k /
+ * to_v of one attention block, all called on `hidden_states` by the caller of LoraInjectedLinear)
+ * run as ONE problem over their concatenated outputs.
+ *   forward : b200lora_lora_gemm on W_cat [nseg*Nseg, K], b200lora_pack_lora(A_cat [r_total, K],
+ *             B_bd [nseg*Nseg, r_total] block diagonal with each layer's scale folded in), scale = 1;
+ *             Y_cat [M, nseg*Nseg] holds the layers' outputs side by side, T_out is [M, r_total].
+ *   backward: the callers' gradients arrive as nseg separate tensors dY[i] [M, Nseg] (row pitch
+ *             ld_dy[i] elements):
+ *     b200lora_linear_bwd_dx_fused  dX = sum_i dY_i·W0_i + (sum_i s_i·dY_i·B_i)·A_cat, dT_out [M, r_total];
+ *                                   Wt = W_catᵀ stored [K, nseg*Nseg]; `pack` as in the forward.
+ *     b200lora_lora_grads_fused     dB[i] += s_i·dY_iᵀ·T[:, ranks of i]   (fp32 [Nseg, r_each[i]])
+ *                                   dA[i] += (dTᵀ·X)[ranks of i]          (fp32 [r_each[i], K])
+ *                                   in ONE launch (nseg + 1 reductions).
+ * 16-bit io only, nseg <= 3, Nseg % 64 == 0, sum of ranks <= 16.
+ */
+int b200lora_linear_bwd_dx_fused(const void* const* dY, const int64_t* ld_dy, int nseg,
+                                 const void* Wt, const void* pack, void* dX, void* dT_out,
+                                 int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                                 b200lora_stream_t stream);
+int b200lora_lora_grads_fused(const void* const* dY, const int64_t* ld_dy, int nseg, const void* X,
+                              const void* T, const void* dT, const float* scales,
+                              float* const* dA, float* const* dB, int64_t M, int K, int Nseg,
+                              const int* r_each, int io_dtype, b200lora_stream_t stream);
+
+/*
  * Weight merge — replaces lora.py:423  `weight + alpha * (up @ down).type(weight.dtype)`
  * (cli_lora_add.py:78 runs it on the CPU).  Wout may alias Win (in-place).
  * up [N,r], down [r,K] in lora_dtype; W in w_dtype.  Rounding follows the reference:
