@@ -128,6 +128,10 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX);
+    if (p.kseg) {
+      tma_prefetch_desc(&tmX1);
+      tma_prefetch_desc(&tmX2);
+    }
     tma_prefetch_desc(&tmWa);
     tma_prefetch_desc(&tmWh);
     tma_prefetch_desc(&tmS1);
@@ -188,6 +192,8 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           cv_w = (rem % p.cv_Wo) * p.cv_str_w - p.cv_pad_w;
         }
         int tap = 0, cb = 0;
+        int sg = 0, sk = 0;                      // K segment and k-block inside it (p.kseg != 0)
+        const CUtensorMap* xm = &tmX;
         for (int kb = 0; kb < p.num_k_blk; ++kb) {
           mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);
           uint8_t* a_dst = stage_base + (size_t)s * stg_bytes;
@@ -203,11 +209,8 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                                     (uint16_t)((tap / p.cv_S) * p.cv_dil_h), pol_x);
               else if (p.kseg == 0)
                 tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
-              else {   // X split along K into equal segments, one tensor each (fused sibling backward)
-                const int sg = kb / p.kseg;
-                const CUtensorMap* xm = sg == 0 ? &tmX : (sg == 1 ? &tmX1 : &tmX2);
-                tma_load_2d_2sm(a_dst, xm, full0, (kb - sg * p.kseg) * BK, m_blk * 256 + (int)rank * BM, pol_x);
-              }
+              else     // X split along K into equal segments, one tensor each (fused sibling backward)
+                tma_load_2d_2sm(a_dst, xm, full0, sk * BK, m_blk * 256 + (int)rank * BM, pol_x);
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
               tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);                  // H rows
@@ -218,6 +221,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           }
           __syncwarp();
           if (++cb == p.cv_cpb) { cb = 0; ++tap; }
+          if (p.kseg && ++sk == p.kseg) { sk = 0; ++sg; xm = sg == 1 ? &tmX1 : &tmX2; }
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       };
