@@ -37,6 +37,10 @@ METRIC = "LoRA-UNet train samples/sec"
 UNIT = "samples/s"
 ATTN_TARGETS = {"CrossAttention", "Attention"}
 WORKLOAD = "sd15_unet_lora_r4_attn_qkvo_64x64_bf16_b8"
+# BASELINE config 3 (--config 3; a parity/coverage configuration, not the headline line): extended
+# injection — resnet Conv2d + time_emb_proj + attention + GEGLU/FeedForward, r = 16
+EXT_TARGETS = {"ResnetBlock2D", "CrossAttention", "Attention", "GEGLU", "FeedForward"}
+WORKLOAD3 = "sd15_unet_lora_r16_extended_conv_attn_ff_64x64_bf16_b8"
 
 
 def peaks():
@@ -162,12 +166,92 @@ def make_batches(n, batch, res, seed, device, pin=False):
     return out
 
 
+class _StockLinear(torch.nn.Module):
+    """lora.py:32-50 evaluated by stock PyTorch ops ON THE GPU (--impl stock_gpu): the number the fused
+    kernels have to beat on the same B200, next to the CPU baseline.  Not a product path."""
+
+    def __init__(self, src, r):
+        super().__init__()
+        self.linear = src
+        self.lora_down = torch.nn.Linear(src.in_features, r, bias=False)
+        self.lora_up = torch.nn.Linear(r, src.out_features, bias=False)
+        self.scale = 1.0
+        torch.nn.init.normal_(self.lora_down.weight, std=1 / r)
+
+    def forward(self, x):
+        return self.linear(x) + self.lora_up(self.lora_down(x)) * self.scale
+
+
+class _StockConv(torch.nn.Module):
+    def __init__(self, src, r):
+        super().__init__()
+        self.conv = src
+        self.lora_down = torch.nn.Conv2d(src.in_channels, r, src.kernel_size, src.stride, src.padding, bias=False)
+        self.lora_up = torch.nn.Conv2d(r, src.out_channels, 1, bias=False)
+        self.scale = 1.0
+        torch.nn.init.normal_(self.lora_down.weight, std=1 / r)
+
+    def forward(self, x):
+        return self.conv(x) + self.lora_up(self.lora_down(x)) * self.scale
+
+
+def _stock_inject(unet, targets, r, convs):
+    import diffusion_finetuning_b200 as L
+    kinds = [torch.nn.Linear, torch.nn.Conv2d] if convs else [torch.nn.Linear]
+    found = list(L._find_modules(unet, targets, search_class=kinds, exclude_children_of=[_StockLinear, _StockConv]))
+    layers, seen = [], set()
+    for parent, name, mod in found:
+        if id(mod) in seen:
+            continue
+        seen.add(id(mod))
+        new = _StockConv(mod, r) if isinstance(mod, torch.nn.Conv2d) else _StockLinear(mod, r)
+        new.to(mod.weight.device)
+        parent._modules[name] = new
+        new.lora_up.weight.requires_grad_(True)
+        new.lora_down.weight.requires_grad_(True)
+        layers.append(new)
+    return layers
+
+
+class StockTrainer:
+    """Same step as Trainer with the reference composition in stock PyTorch on the GPU."""
+
+    def __init__(self, device, rank_r, extended=False):
+        from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
+        torch.manual_seed(0)
+        self.unet = UNet2DConditionModel().to(device)
+        self.unet.requires_grad_(False)
+        self.layers = _stock_inject(self.unet, EXT_TARGETS if extended else ATTN_TARGETS, rank_r, extended)
+        self.n_layers = len(self.layers)
+        g = torch.Generator(device="cpu").manual_seed(1)
+        with torch.no_grad():
+            for m in self.layers:
+                m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
+        self.params = [p for m in self.layers for p in (m.lora_up.weight, m.lora_down.weight)]
+        self.opt = torch.optim.AdamW(self.params, lr=1e-4, fused=True)
+        self.device = device
+
+    def step(self, b):
+        self.opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            pred = self.unet(b["latents"], b["t"], b["ctx"])
+        loss = F.mse_loss(pred.float(), b["target"].float(), reduction="mean")
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(self.params, 1.0)
+        self.opt.step()
+        return loss
+
+    def step_from_host(self, hb):
+        b = {k: v.to(self.device, non_blocking=True) for k, v in hb.items()}
+        return self.step(b).item()
+
+
 class Trainer:
     """The public API a user of the reference calls, end to end: inject_trainable_lora ->
     optimizer over the returned parameter generators -> fwd/bwd/clip/step
     (train_lora_dreambooth.py:595-676, 816-888)."""
 
-    def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True):
+    def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True, extended=False):
         import itertools
         import diffusion_finetuning_b200 as L
         from diffusion_finetuning_b200 import dp
@@ -178,12 +262,15 @@ class Trainer:
             self.unet.to(memory_format=torch.channels_last)
         self.channels_last = channels_last
         self.unet.requires_grad_(False)
-        params, names = L.inject_trainable_lora(self.unet, ATTN_TARGETS, r=rank_r)
+        if extended:
+            params, names = L.inject_trainable_lora_extended(self.unet, EXT_TARGETS, r=rank_r)
+        else:
+            params, names = L.inject_trainable_lora(self.unet, ATTN_TARGETS, r=rank_r)
         self.n_layers = len(names)
         g = torch.Generator(device="cpu").manual_seed(1)
         with torch.no_grad():                     # non-zero up so every gradient is live
             for m in self.unet.modules():
-                if isinstance(m, L.LoraInjectedLinear):
+                if isinstance(m, (L.LoraInjectedLinear, L.LoraInjectedConv2d)):
                     m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
         self.groups = L.fuse_sibling_projections(self.unet) if fuse else []
         self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
@@ -232,7 +319,7 @@ def timed(fn, steps, dist_on, device):
 # ------------------------------------------------------------------------------------------------
 # CPU leg: the reference algorithm (oracle restatement of lora.py:32-50, 137-183) on host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_leg(steps, warmup, batch, res, rank_r):
+def cpu_leg(steps, warmup, batch, res, rank_r, extended=False):
     import itertools
     from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
     from oracle import lora_oracle as O
@@ -241,7 +328,7 @@ def cpu_leg(steps, warmup, batch, res, rank_r):
     torch.manual_seed(0)
     unet = UNet2DConditionModel()
     unet.requires_grad_(False)
-    layers = O.inject(unet, ATTN_TARGETS, r=rank_r)
+    layers = O.inject(unet, EXT_TARGETS if extended else ATTN_TARGETS, r=rank_r, convs=extended)
     g = torch.Generator().manual_seed(1)
     with torch.no_grad():
         for m in layers:
@@ -275,7 +362,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    cb = cpu_leg(args.steps, max(1, min(args.warmup, 2)), 1, args.res, args.rank)
+    cb = cpu_leg(args.steps, max(1, min(args.warmup, 2)), 1, args.res, args.rank, args.config == 3)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -288,8 +375,9 @@ def run_reference(args):
 
 
 def config_dict(args, batch):
-    return {"workload": WORKLOAD, "unet": "SD-1.5 shape (320,640,1280,1280), 2 layers/block, ctx 77x768",
-            "lora": f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out", "latents": f"{args.res}x{args.res}",
+    return {"workload": WORKLOAD3 if getattr(args, "config", 2) == 3 else WORKLOAD, "unet": "SD-1.5 shape (320,640,1280,1280), 2 layers/block, ctx 77x768",
+            "lora": (f"r={args.rank} extended: resnet convs, time_emb_proj, attention, GEGLU/FeedForward"
+                     if getattr(args, "config", 2) == 3 else f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out"), "latents": f"{args.res}x{args.res}",
             "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
             "optimizer": "AdamW lr 1e-4, clip 1.0", "memory_format": getattr(args, "memory_format", "nchw"),
             "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch",
@@ -301,17 +389,21 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "stock_gpu"])
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--res", type=int, default=64)
     ap.add_argument("--rank", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3],
+                    help="BASELINE config: 2 = attention q/k/v/out r=4 (the headline), 3 = extended r=16 with resnet convs")
     ap.add_argument("--no-fuse", action="store_true",
                     help="run q/k/v LoRA layers one launch each instead of fused per attention block")
     ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
                     help="memory format of the frozen stock-PyTorch UNet (the reference scripts use nchw)")
     ap.add_argument("--breakdown", default=None, help="write the per-kernel breakdown JSON here")
     args = ap.parse_args()
+    if args.config == 3 and args.rank == 4:
+        args.rank = 16
     if args.impl == "reference":
         return run_reference(args)
     args.warmup = max(args.warmup, 3)
@@ -336,7 +428,28 @@ def main():
     from diffusion_finetuning_b200 import ops
     nat.lib()
 
-    tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last", fuse=not args.no_fuse)
+    if args.impl == "stock_gpu":
+        # evidence line for profiles/: the reference composition in stock PyTorch on the same GPU
+        tr = StockTrainer(device, args.rank, extended=args.config == 3)
+        pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
+        host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
+        for i in range(args.warmup):
+            tr.step(pool[i % 4])
+        t_dev = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
+        t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
+        if rank == 0:
+            samples = args.batch * world * args.steps
+            print(json.dumps({"impl": "stock_gpu", "metric": METRIC, "value": samples / t_dev, "unit": UNIT,
+                              "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                              "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "dtype": "bf16",
+                              "data": "synthetic", "config": config_dict(args, args.batch),
+                              "e2e": {"value": samples / t_e2e, "unit": UNIT}, "gpu_launches": 0,
+                              "lora_layers": tr.n_layers,
+                              "note": "lora.py:49-50 as 3 F.linear + mul + add (conv: 3 convs) in stock PyTorch, "
+                                      "autograd backward, same UNet / optimizer / clip; single process"}), flush=True)
+        return 0
+    tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last", fuse=not args.no_fuse,
+                 extended=args.config == 3)
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
     for i in range(args.warmup):
@@ -410,7 +523,7 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         del tr, pool
         torch.cuda.empty_cache()
-        cb = cpu_leg(3, 1, 1, args.res, args.rank)
+        cb = cpu_leg(3, 1, 1, args.res, args.rank, args.config == 3)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     print(json.dumps(line), flush=True)
     if dist_on:
