@@ -39,7 +39,7 @@ cudaError_t launch_conv_pack(const void*, const void*, int, const void*, int, vo
                              int, int, int, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_conv_zcat(const void*, const void*, int, float, void*, void*, long long, int, int,
                              int, int, int, cudaStream_t);
-cudaError_t launch_conv_dA(const void*, const void*, float, float*, const int*, int, int, cudaStream_t);
+
 template <typename TIO>
 cudaError_t launch_conv_zcat_tc(const CUtensorMap*, const CUtensorMap*, const void*, int, float, void*, void*,
                                 long long, int, int, int, int, int, cudaStream_t);
@@ -689,9 +689,9 @@ extern "C" int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float 
   if (!di.ok || di.major != 10) { set_error("conv2d_grad_a needs an sm_100 device"); return B200LORA_E_CUDA; }
   if (!aligned16(X_nhwc)) { set_error("conv2d_grad_a needs a 16-byte aligned X"); return B200LORA_E_ALIGN; }
   CUtensorMap tmX;
-  int rc = get_tmap_im2col(&tmX, X_nhwc, N, H, W, C, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w, io_dtype);
-  if (rc) return rc;
+  int rc;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if ((rc = get_tmap_im2col(&tmX, X_nhwc, N, H, W, C, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w, io_dtype))) return rc;
   cudaError_t e = io_dtype == B200LORA_BF16
                       ? launch_conv_grad_a_tc<__nv_bfloat16>(&tmX, dT, scale, dA, geo, r, di.sms, stream)
                       : launch_conv_grad_a_tc<__half>(&tmX, dT, scale, dA, geo, r, di.sms, stream);

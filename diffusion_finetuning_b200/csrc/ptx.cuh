@@ -109,6 +109,29 @@ __device__ __forceinline__ void mma_16816<__half>(float (&d)[4], const uint32_t 
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// B fragment of P[tok0 .. tok0+16, 8*jh .. 8*jh+8): lane (g = lane/4, t = lane%4) holds
+// (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero.
+// `P` points at the problem's first rank column, `ldp` is the row stride in elements.
+__device__ __forceinline__ void load_p_frag(const unsigned short* __restrict__ P, long long tok0,
+                                            int j, int r, int ldp, long long M, int t, uint32_t (&b)[2]) {
+  b[0] = 0u; b[1] = 0u;
+  if (j < r) {
+    const long long k0 = tok0 + 2 * t;
+    if (k0 + 9 < M) {
+      const unsigned short* q = P + k0 * ldp + j;
+      b[0] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + ldp) << 16);
+      b[1] = (uint32_t)__ldg(q + 8 * ldp) | ((uint32_t)__ldg(q + 9 * ldp) << 16);
+    } else {
+      uint32_t e[4];
+      const int off[4] = {0, 1, 8, 9};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) e[i] = (k0 + off[i] < M) ? (uint32_t)__ldg(P + (k0 + off[i]) * ldp + j) : 0u;
+      b[0] = e[0] | (e[1] << 16);
+      b[1] = e[2] | (e[3] << 16);
+    }
+  }
+}
+
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&a)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
                : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3])

@@ -190,29 +190,6 @@ constexpr int SMEM_BYTES = NS * STAGE_BYTES + 1024;
 constexpr int CTAS_PER_SM = 3;
 }
 
-// B fragment of P[tok0 .. tok0+16, 8*jh .. 8*jh+8): lane (g = lane/4, t = lane%4) holds
-// (P[2t][g], P[2t+1][g]) and (P[2t+8][g], P[2t+9][g]); rows >= M and ranks >= r read as zero.
-// `P` points at the problem's first rank column, `ldp` is the row stride in elements.
-__device__ __forceinline__ void load_p_frag(const unsigned short* __restrict__ P, long long tok0,
-                                            int j, int r, int ldp, long long M, int t, uint32_t (&b)[2]) {
-  b[0] = 0u; b[1] = 0u;
-  if (j < r) {
-    const long long k0 = tok0 + 2 * t;
-    if (k0 + 9 < M) {
-      const unsigned short* q = P + k0 * ldp + j;
-      b[0] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + ldp) << 16);
-      b[1] = (uint32_t)__ldg(q + 8 * ldp) | ((uint32_t)__ldg(q + 9 * ldp) << 16);
-    } else {
-      uint32_t e[4];
-      const int off[4] = {0, 1, 8, 9};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) e[i] = (k0 + off[i] < M) ? (uint32_t)__ldg(P + (k0 + off[i]) * ldp + j) : 0u;
-      b[0] = e[0] | (e[1] << 16);
-      b[1] = e[2] | (e[3] << 16);
-    }
-  }
-}
-
 // One reduction problem of a launch: G[c, j] = scale * sum_m Z[m, c] * P[m, j0 + j], j < r.
 // Ranks [r_off[d], r_off[d+1]) go to out[d] (several destinations = the dA rows of fused siblings).
 struct RedTcProb {
