@@ -251,7 +251,8 @@ class Trainer:
     optimizer over the returned parameter generators -> fwd/bwd/clip/step
     (train_lora_dreambooth.py:595-676, 816-888)."""
 
-    def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True, extended=False):
+    def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True, extended=False,
+                 capturable=False):
         import itertools
         import diffusion_finetuning_b200 as L
         from diffusion_finetuning_b200 import dp
@@ -275,11 +276,20 @@ class Trainer:
         self.groups = L.fuse_sibling_projections(self.unet) if fuse else []
         self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
         self.arena.broadcast_params(0)
-        self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True)
+        self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True, capturable=capturable)
         self.device = device
         self.autocast = autocast
+        self.graphed = None
+
+    def capture(self, example_batch):
+        """Whole step as one CUDA graph (dp.GraphedStep); step()/step_from_host() replay it from then on."""
+        from diffusion_finetuning_b200 import dp
+        self.graphed = dp.GraphedStep(self.eager_step, example_batch)
 
     def step(self, b):
+        return self.graphed(b) if self.graphed is not None else self.eager_step(b)
+
+    def eager_step(self, b):
         self.arena.zero()
         lat = b["latents"].contiguous(memory_format=torch.channels_last) if self.channels_last else b["latents"]
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.autocast):
@@ -292,6 +302,8 @@ class Trainer:
         return loss
 
     def step_from_host(self, hb):
+        if self.graphed is not None:            # pinned host batch -> the graph's static inputs -> replay
+            return self.graphed(hb).item()
         b = {k: v.to(self.device, non_blocking=True) for k, v in hb.items()}
         return self.step(b).item()              # D2H read of the loss every step
 
@@ -370,7 +382,7 @@ def run_reference(args):
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -380,6 +392,7 @@ def config_dict(args, batch):
                      if getattr(args, "config", 2) == 3 else f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out"), "latents": f"{args.res}x{args.res}",
             "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
             "optimizer": "AdamW lr 1e-4, clip 1.0", "memory_format": getattr(args, "memory_format", "nchw"),
+            "step_launch": "python" if getattr(args, "no_graph", False) else "whole step replayed as one CUDA graph",
             "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch",
             "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
 
@@ -396,6 +409,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--config", type=int, default=2, choices=[2, 3],
                     help="BASELINE config: 2 = attention q/k/v/out r=4 (the headline), 3 = extended r=16 with resnet convs")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="enqueue every step from Python instead of replaying the captured CUDA graph")
     ap.add_argument("--no-fuse", action="store_true",
                     help="run q/k/v LoRA layers one launch each instead of fused per attention block")
     ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
@@ -439,19 +454,21 @@ def main():
         t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
         if rank == 0:
             samples = args.batch * world * args.steps
-            print(json.dumps({"impl": "stock_gpu", "metric": METRIC, "value": samples / t_dev, "unit": UNIT,
+            _emit({"impl": "stock_gpu", "metric": METRIC, "value": samples / t_dev, "unit": UNIT,
                               "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                               "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "dtype": "bf16",
                               "data": "synthetic", "config": config_dict(args, args.batch),
                               "e2e": {"value": samples / t_e2e, "unit": UNIT}, "gpu_launches": 0,
                               "lora_layers": tr.n_layers,
                               "note": "lora.py:49-50 as 3 F.linear + mul + add (conv: 3 convs) in stock PyTorch, "
-                                      "autograd backward, same UNet / optimizer / clip; single process"}), flush=True)
+                                      "autograd backward, same UNet / optimizer / clip; single process"})
         return 0
     tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last", fuse=not args.no_fuse,
-                 extended=args.config == 3)
+                 extended=args.config == 3, capturable=not args.no_graph)
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
+    if not args.no_graph:
+        tr.capture(pool[0])                     # 3 eager warm-up steps + capture
     for i in range(args.warmup):
         tr.step(pool[i % 4])
     tr.step_from_host(host_pool[0])
@@ -465,12 +482,14 @@ def main():
     l0 = nat.LAUNCHES
     t_dev = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
     launches = nat.LAUNCHES - l0
+    if tr.graphed is not None:                  # replays do not pass through Python: count what was captured
+        launches = tr.graphed.kernel_launches * args.steps
     # ---- timed region 2: end to end from pinned host memory, loss read back every step ----
     t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
     # ---- region 3: the same K steps with CUDA events around every launch of our kernels (roofline);
     # kept out of region 1 because an event between two launches defeats their programmatic overlap ----
     ops.PROFILER = prof
-    t_prof = timed(lambda i: tr.step(pool[i % 4]), args.steps, dist_on, device)
+    t_prof = timed(lambda i: tr.eager_step(pool[i % 4]), args.steps, dist_on, device)
     ops.PROFILER = None
     clk = clocks.stop() if rank == 0 else None
 
@@ -525,11 +544,29 @@ def main():
         torch.cuda.empty_cache()
         cb = cpu_leg(3, 1, 1, args.res, args.rank, args.config == 3)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if dist_on:
         dist.destroy_process_group()
     return 0
 
 
+def _emit(obj):
+    """The ONE JSON line goes to the process's real stdout; everything else that lands on fd 1 while the
+    run lasts (NCCL's version banner, library chatter) was re-pointed at stderr by _quiet_stdout()."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(obj) + "\n").encode())
+
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
 if __name__ == "__main__":
+    _quiet_stdout()
     sys.exit(main())

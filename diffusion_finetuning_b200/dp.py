@@ -94,6 +94,7 @@ class LoraGradArena:
         self._hooks = []
         self._sync = True
         self._comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        self._comm_used = False
         for p, layer in entries:
             o, n, bi = self._slot[id(p)]
             view = self.flat[o:o + n].view_as(p)
@@ -151,6 +152,7 @@ class LoraGradArena:
         nccl = self._comm is not None
         op = dist.ReduceOp.AVG if (nccl and self.average) else dist.ReduceOp.SUM
         if nccl:
+            self._comm_used = True
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm):
@@ -195,8 +197,11 @@ class LoraGradArena:
             if b.work is not None:
                 b.work.wait()
                 b.work = None
-        if self._comm is not None:
+        if self._comm is not None and self._comm_used:
+            # (only when something ran there this step: under CUDA-graph capture a stream that never
+            # joined the capture must not be waited on)
             torch.cuda.current_stream(self.device).wait_stream(self._comm)
+            self._comm_used = False
         if self.world > 1 and self.average and self._comm is None:
             self.flat.mul_(1.0 / self.world)        # gloo has no AVG
         for dt, lp in self._lowp.items():
@@ -238,3 +243,43 @@ class LoraGradArena:
         for layer in self._layers:
             if isinstance(layer, LoraInjectedLinear):
                 layer._grad_sink = None
+
+
+class GraphedStep:
+    """A whole training step — arena.zero(), forward, backward (with the bucketed exchange on its side
+    stream), clip, optimizer — captured ONCE as a CUDA graph and replayed.
+
+    Why: the LoRA step of an SD-1.5 UNet is ~3000 kernel launches; the host needs ~50 ms to enqueue them
+    against ~55 ms of GPU work, so any host jitter (8 ranks sharing the cores of one node) shows up as
+    step time.  Replaying a graph takes the host out of the loop; the kernels, their streams and their
+    programmatic-launch edges are the ones the eager step issued.
+
+    `step_fn(batch_dict) -> loss tensor` must be free of host synchronisation (no .item(), optimizer
+    built with capturable=True) and shape-static.  Inputs are copied into static buffers before every
+    replay; the returned loss tensor is overwritten by each replay.  Caches keyed on parameter versions
+    (the LoRA packs) are refreshed INSIDE the captured step because the warm-up steps' optimizer
+    updates invalidated them, so every replay re-packs from the live parameters.
+    """
+
+    def __init__(self, step_fn, example_batch: dict, warmup: int = 3):
+        dev = next(iter(example_batch.values())).device
+        self.static = {k: v.clone() for k, v in example_batch.items()}
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                step_fn(self.static)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        from . import _native as nat
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = nat.LAUNCHES
+        with torch.cuda.graph(self.graph):
+            self.loss = step_fn(self.static)
+        self.kernel_launches = nat.LAUNCHES - n0     # C-ABI launches captured = launched per replay
+
+    def __call__(self, batch: dict):
+        for k, v in batch.items():
+            self.static[k].copy_(v, non_blocking=True)
+        self.graph.replay()
+        return self.loss

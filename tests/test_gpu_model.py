@@ -191,3 +191,58 @@ def test_config4_clip_text_encoder_matches_oracle(mode):
     # dX of every layer reaches the embedding table: rows of the placeholder tokens agree
     ge, gr = ours.get_input_embeddings().weight.grad, ref.get_input_embeddings().weight.grad
     assert rel_err(ge[1000:1002], gr[1000:1002]) < tol_g
+
+
+def test_graphed_training_step_equals_eager():
+    """dp.GraphedStep: the whole step (zero, fwd, bwd, exchange, clip, AdamW) replayed as one CUDA graph
+    walks the same loss / parameter trajectory as the eager step, with fresh inputs every replay."""
+    import copy
+    import itertools
+    from diffusion_finetuning_b200 import dp
+
+    def build():
+        torch.manual_seed(0)
+        unet = UNet2DConditionModel.tiny().to(DEV)
+        unet.requires_grad_(False)
+        torch.manual_seed(1)
+        params, _ = L.inject_trainable_lora(unet, {"CrossAttention", "Attention"}, r=4)
+        g = torch.Generator().manual_seed(2)
+        with torch.no_grad():
+            for m in unet.modules():
+                if isinstance(m, L.LoraInjectedLinear):
+                    m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(DEV))
+        L.fuse_sibling_projections(unet)
+        arena = dp.LoraGradArena(unet)
+        opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-3, fused=True, capturable=True)
+
+        def step(b):
+            arena.zero()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                pred = unet(b["latents"], b["t"], b["ctx"])
+            loss = torch.nn.functional.mse_loss(pred.float(), b["target"])
+            loss.backward()
+            arena.finish()
+            arena.clip_grad_norm_(1.0)
+            opt.step()
+            return loss
+        return unet, step
+
+    ctx_dim = 32
+    g = torch.Generator().manual_seed(3)
+    batches = [dict(latents=torch.randn(2, 4, 32, 32, generator=g).to(DEV), t=torch.randint(0, 1000, (2,), generator=g).to(DEV),
+                    ctx=torch.randn(2, 77, ctx_dim, generator=g).to(DEV), target=torch.randn(2, 4, 32, 32, generator=g).to(DEV))
+               for _ in range(5)]
+    ue, step_e = build()
+    ug, step_g = build()
+    warm = 3
+    for i in range(warm):                       # GraphedStep's own warm-up runs 3 steps on its first batch
+        step_e(batches[0])
+    graphed = dp.GraphedStep(step_g, batches[0], warmup=warm)
+    assert graphed.kernel_launches > 0
+    for b in batches:
+        le = step_e(b).item()
+        lg = graphed(b).item()
+        assert abs(le - lg) <= 2e-2 * abs(le), (le, lg)
+    for pe, pg in zip(ue.parameters(), ug.parameters()):
+        if pe.requires_grad:      # Adam normalises: a gradient whose sign is rounding noise moves a weight by +-lr
+            assert rel_err(pg, pe) < 0.15
