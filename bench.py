@@ -493,9 +493,13 @@ def main():
     ops.PROFILER = None
     clk = clocks.stop() if rank == 0 else None
 
+    # All ranks are done with the GPU.  Drop the captured graph (it holds NCCL work) and leave through
+    # _leave(): tearing a communicator down under a live graph can block at interpreter exit.
+    tr.graphed = None
+    torch.cuda.synchronize(device)
+    if dist_on:
+        dist.barrier()
     if rank != 0:
-        if dist_on:
-            dist.destroy_process_group()
         return 0
 
     pk = peaks()
@@ -545,8 +549,6 @@ def main():
         cb = cpu_leg(3, 1, 1, args.res, args.rank, args.config == 3)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     _emit(line)
-    if dist_on:
-        dist.destroy_process_group()
     return 0
 
 
@@ -567,6 +569,14 @@ def _quiet_stdout():
         os.dup2(2, 1)
 
 
+def _leave(rc):
+    """Flush and exit without interpreter teardown (NCCL communicators / CUDA graphs are process-lifetime
+    objects here; the driver only needs the exit code and the JSON line)."""
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(int(rc or 0))
+
+
 if __name__ == "__main__":
     _quiet_stdout()
-    sys.exit(main())
+    _leave(main())
