@@ -146,6 +146,22 @@ class LaunchProfiler:
             s["bytes"] += by
         return out
 
+    def by_shape(self, peak_tf, peak_gbs):
+        """Per (kind, M, K, N, r): launches, mean event-bracketed duration, achieved TFLOP/s and GB/s."""
+        acc = {}
+        for kind, M, K, N, r, e, a, b in self.recs:
+            fl, by = self.work(kind, M, K, N, r, e)
+            s = acc.setdefault((kind, M, K, N, r), [0, 0.0, fl, by])
+            s[0] += 1
+            s[1] += a.elapsed_time(b)
+        rows = []
+        for (kind, M, K, N, r), (n, ms, fl, by) in sorted(acc.items(), key=lambda kv: -kv[1][1]):
+            us = ms * 1e3 / n
+            rows.append({"kind": kind, "M": M, "K": K, "N": N, "r": r, "launches": n, "avg_us": round(us, 2),
+                         "tflops": round(fl / us / 1e6, 1), "gbs": round(by / us / 1e3, 1),
+                         "frac_tensor": round(fl / us / 1e6 / peak_tf, 3), "frac_hbm": round(by / us / 1e3 / peak_gbs, 3)})
+        return rows
+
 
 # ------------------------------------------------------------------------------------------------
 # the training job
@@ -216,10 +232,13 @@ def _stock_inject(unet, targets, r, convs):
 class StockTrainer:
     """Same step as Trainer with the reference composition in stock PyTorch on the GPU."""
 
-    def __init__(self, device, rank_r, extended=False):
+    def __init__(self, device, rank_r, extended=False, channels_last=False):
         from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
         torch.manual_seed(0)
         self.unet = UNet2DConditionModel().to(device)
+        if channels_last:
+            self.unet.to(memory_format=torch.channels_last)
+        self.channels_last = channels_last
         self.unet.requires_grad_(False)
         self.layers = _stock_inject(self.unet, EXT_TARGETS if extended else ATTN_TARGETS, rank_r, extended)
         self.n_layers = len(self.layers)
@@ -233,8 +252,9 @@ class StockTrainer:
 
     def step(self, b):
         self.opt.zero_grad(set_to_none=True)
+        lat = b["latents"].contiguous(memory_format=torch.channels_last) if self.channels_last else b["latents"]
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            pred = self.unet(b["latents"], b["t"], b["ctx"])
+            pred = self.unet(lat, b["t"], b["ctx"])
         loss = F.mse_loss(pred.float(), b["target"].float(), reduction="mean")
         loss.backward()
         torch.nn.utils.clip_grad_norm_(self.params, 1.0)
@@ -445,7 +465,8 @@ def main():
 
     if args.impl == "stock_gpu":
         # evidence line for profiles/: the reference composition in stock PyTorch on the same GPU
-        tr = StockTrainer(device, args.rank, extended=args.config == 3)
+        tr = StockTrainer(device, args.rank, extended=args.config == 3,
+                          channels_last=args.memory_format == "channels_last")
         pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
         host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
         for i in range(args.warmup):
@@ -468,7 +489,14 @@ def main():
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
     if not args.no_graph:
-        tr.capture(pool[0])                     # 3 eager warm-up steps + capture
+        try:
+            tr.capture(pool[0])                 # 3 eager warm-up steps + capture
+        except Exception as exc:                # same kernels either way: only the launch mechanism changes
+            print(f"[bench] CUDA-graph capture failed ({type(exc).__name__}: {exc}); enqueueing steps from Python",
+                  file=sys.stderr)
+            tr.graphed = None
+            args.no_graph = True
+            torch.cuda.synchronize(device)
     for i in range(args.warmup):
         tr.step(pool[i % 4])
     tr.step_from_host(host_pool[0])
@@ -524,6 +552,7 @@ def main():
         roofline["grads_kernel"] = {"bound": "hbm", "achieved": s["bytes"] / (s["ms"] * 1e-3) / 1e9, "peak": pk["hbm"],
                                     "unit": "GB/s", "frac": s["bytes"] / (s["ms"] * 1e-3) / 1e9 / pk["hbm"],
                                     "share_of_step": s["ms"] / args.steps / step_ms}
+    roofline["by_shape"] = prof.by_shape(pk["tf_sustained"], pk["hbm"])
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
