@@ -160,9 +160,13 @@ def _clip_pair(r=4, layers=2):
     return ref, ours.to(DEV), ref_layers, our_layers
 
 
-@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("mode", ["fp32", "bf16", "bf16-fused"])
 def test_config4_clip_text_encoder_matches_oracle(mode):
     ref, ours, ref_layers, our_layers = _clip_pair()
+    groups = L.fuse_sibling_projections(ours) if mode == "bf16-fused" else []      # q_proj/k_proj/v_proj
+    if groups:
+        assert len(groups) == 2 and all(len(g.layers) == 3 for g in groups)
+        mode = "bf16"
     ids = torch.randint(0, 1000, (8, 77), generator=torch.Generator().manual_seed(3))
     ids[:, 4], ids[:, 5] = 1000, 1001                       # the two placeholder tokens
     tol_y, tol_g = (1e-4, 1e-3) if mode == "fp32" else (2e-2, 5e-2)
@@ -181,7 +185,10 @@ def test_config4_clip_text_encoder_matches_oracle(mode):
     torch.nn.functional.mse_loss(y.float(), target.to(DEV)).backward()
     torch.nn.functional.mse_loss(yr.float(), target).backward()
     assert rel_err(y, yr.float()) < tol_y, rel_err(y, yr.float())
-    assert nat.LAUNCHES - before >= 3 * len(our_layers)     # fwd + bwd-dX + reductions per layer, all native
+    if groups:
+        assert all(g.fused_calls == 1 and g.enabled for g in groups)
+    else:
+        assert nat.LAUNCHES - before >= 3 * len(our_layers)     # fwd + bwd-dX + reductions per layer, all native
     worst = 0.0
     for a, b in zip(ref_layers, our_layers):
         assert b.lora_up.weight.grad is not None and b.lora_down.weight.grad is not None
