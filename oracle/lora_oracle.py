@@ -9,8 +9,9 @@ import this module, and only as the checker or the timed CPU baseline; the produ
 Pinning: the reference ships NO tests or golden vectors for this path.  The oracle is
 pinned by (a) `oracle/make_golden.py`, which imports the real reference `lora.py` in the build
 container and commits its outputs on seeded inputs to `tests/golden/`, and (b)
-`tests/test_oracle_vs_reference.py`, which runs the oracle against the reference directly whenever
-`/root/reference` is present.  The Conv2d / selector / dropout surface does not exist in the
+`tests/test_oracle_golden.py` (oracle vs those vectors) and `tests/test_api_host.py::
+test_against_reference_directly`, which runs against the reference itself whenever `/root/reference`
+is present.  The Conv2d / selector / dropout surface does not exist in the
 reference snapshot: for it the oracle restates upstream cloneofsimo/lora semantics as specified in
 SURVEY §8(c) — **parity unpinned by the reference** for those rows.
 """
