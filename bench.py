@@ -272,7 +272,7 @@ class Trainer:
     (train_lora_dreambooth.py:595-676, 816-888)."""
 
     def __init__(self, device, rank_r, autocast=True, channels_last=False, fuse=True, extended=False,
-                 capturable=False):
+                 capturable=False, arena_optimizer=False):
         import itertools
         import diffusion_finetuning_b200 as L
         from diffusion_finetuning_b200 import dp
@@ -296,7 +296,11 @@ class Trainer:
         self.groups = L.fuse_sibling_projections(self.unet) if fuse else []
         self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
         self.arena.broadcast_params(0)
-        self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True, capturable=capturable)
+        if arena_optimizer:      # clip 1.0 + AdamW over the flat arenas: one C-ABI call per step
+            self.opt = dp.ArenaAdamW(self.arena, lr=1e-4, weight_decay=1e-2, max_grad_norm=1.0)
+        else:
+            self.opt = torch.optim.AdamW(itertools.chain(*params), lr=1e-4, fused=True, capturable=capturable)
+        self.arena_optimizer = arena_optimizer
         self.device = device
         self.autocast = autocast
         self.graphed = None
@@ -317,7 +321,8 @@ class Trainer:
         loss = F.mse_loss(pred.float(), b["target"].float(), reduction="mean")
         loss.backward()
         self.arena.finish()
-        self.arena.clip_grad_norm_(1.0)
+        if not self.arena_optimizer:
+            self.arena.clip_grad_norm_(1.0)
         self.opt.step()
         return loss
 
@@ -411,7 +416,7 @@ def config_dict(args, batch):
             "lora": (f"r={args.rank} extended: resnet convs, time_emb_proj, attention, GEGLU/FeedForward"
                      if getattr(args, "config", 2) == 3 else f"r={args.rank} on CrossAttention to_q/to_k/to_v/to_out"), "latents": f"{args.res}x{args.res}",
             "batch_per_gpu": batch, "precision": "bf16 autocast, fp32 masters", "parallelism": f"dp{args.gpus}",
-            "optimizer": "AdamW lr 1e-4, clip 1.0", "memory_format": getattr(args, "memory_format", "nchw"),
+            "optimizer": "AdamW lr 1e-4, clip 1.0" + (" (dp.ArenaAdamW)" if getattr(args, "arena_optimizer", False) else ""), "memory_format": getattr(args, "memory_format", "nchw"),
             "step_launch": "python" if getattr(args, "no_graph", False) else "whole step replayed as one CUDA graph",
             "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch",
             "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
@@ -431,6 +436,9 @@ def main():
                     help="BASELINE config: 2 = attention q/k/v/out r=4 (the headline), 3 = extended r=16 with resnet convs")
     ap.add_argument("--no-graph", action="store_true",
                     help="enqueue every step from Python instead of replaying the captured CUDA graph")
+    ap.add_argument("--arena-optimizer", action="store_true",
+                    help="dp.ArenaAdamW (clip + AdamW over the flat arenas, one C-ABI call) instead of "
+                         "arena.clip_grad_norm_ + torch fused AdamW; measured equal within run-to-run noise")
     ap.add_argument("--no-fuse", action="store_true",
                     help="run q/k/v LoRA layers one launch each instead of fused per attention block")
     ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
@@ -485,7 +493,8 @@ def main():
                                       "autograd backward, same UNet / optimizer / clip; single process"})
         return 0
     tr = Trainer(device, args.rank, channels_last=args.memory_format == "channels_last", fuse=not args.no_fuse,
-                 extended=args.config == 3, capturable=not args.no_graph)
+                 extended=args.config == 3, capturable=not args.no_graph,
+                 arena_optimizer=args.arena_optimizer)
     pool = make_batches(4, args.batch, args.res, 1234 + rank, device)
     host_pool = make_batches(4, args.batch, args.res, 4321 + rank, None, pin=True)
     if not args.no_graph:

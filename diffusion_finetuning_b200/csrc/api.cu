@@ -66,6 +66,8 @@ cudaError_t launch_merge(const void*, void*, const void*, const void*, float, in
                          float*, cudaStream_t);
 cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, int, int,
                                 cudaStream_t);
+cudaError_t launch_arena_adamw(float*, float*, float*, float*, long long, float, float, float, float, float,
+                               float, float*, cudaStream_t);
 
 // ---------------------------------------------------------------------------------------
 // device info
@@ -762,6 +764,19 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
   else RUN(__nv_bfloat16);
 #undef RUN
   if (e != cudaSuccess) { set_error("lora_grads launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_arena_adamw(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                    float lr, float beta1, float beta2, float eps, float weight_decay,
+                                    float max_grad_norm, float* scratch, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !scratch) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (n <= 0) return 0;
+  if ((reinterpret_cast<uintptr_t>(grads) & 15) != 0) { set_error("arena_adamw needs a 16-byte aligned gradient arena"); return B200LORA_E_ALIGN; }
+  cudaError_t e = launch_arena_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
+                                     max_grad_norm, scratch, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("arena_adamw launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

@@ -283,3 +283,89 @@ class GraphedStep:
             self.static[k].copy_(v, non_blocking=True)
         self.graph.replay()
         return self.loss
+
+
+class ArenaAdamW:
+    """Global-norm clip + AdamW over the flat arenas in one C-ABI call.
+
+    Replaces `clip_grad_norm_(params, max_norm)` + `torch.optim.AdamW(params).step()`
+    (train_lora_dreambooth.py:676, 878-888; cli_lora_pti.py:448-451) for the LoRA parameters of a
+    `LoraGradArena`.  The parameters are re-homed into ONE flat fp32 buffer laid out exactly like the
+    gradient arena (`p.data` becomes a view of it; the Parameter objects, and so every reference the
+    modules, the optimizer-free training loop and `save_lora_weight` hold, stay the same), so the
+    update is two kernels over contiguous memory instead of ~250 small tensors.  The step count lives
+    on the device: the whole step stays CUDA-graph capturable.
+
+    fp32 parameters only (fp32 masters under autocast, the reference's mixed-precision mode); anything
+    else raises — there is no per-tensor fallback.
+    """
+
+    def __init__(self, arena: "LoraGradArena", lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2, max_grad_norm: Optional[float] = None):
+        from . import _native as nat
+        if arena.device.type != "cuda":
+            raise nat.B200LoraError("ArenaAdamW runs on the b200lora kernels: CUDA arena required (no CPU fallback)")
+        for p in arena.params:
+            if p.dtype != torch.float32:
+                raise nat.B200LoraError(f"ArenaAdamW needs fp32 LoRA parameters (got {p.dtype}); keep fp32 masters "
+                                        "and run the model under autocast")
+        self.arena = arena
+        self.lr, self.betas, self.eps, self.weight_decay = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        self.max_grad_norm = None if max_grad_norm is None else float(max_grad_norm)
+        n = arena.flat.numel()
+        self.flat_p = torch.empty(n, dtype=torch.float32, device=arena.device)
+        with torch.no_grad():
+            for p in arena.params:                     # same offsets as the gradient arena
+                o, cnt, _ = arena._slot[id(p)]
+                self.flat_p[o:o + cnt].copy_(p.detach().reshape(-1))
+                p.data = self.flat_p[o:o + cnt].view_as(p)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=arena.device)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=arena.device)
+        self.scratch = torch.zeros(2, dtype=torch.float32, device=arena.device)   # [sum g^2, step count]
+
+    def _check_homes(self):
+        # monkeypatch_* / weight loading re-assign `.weight` with fresh Parameters: the arena (and this
+        # optimizer) must be rebuilt after that, exactly as a torch optimizer would have to be
+        for p in self.arena.params:
+            o, cnt, _ = self.arena._slot[id(p)]
+            if p.data_ptr() != self.flat_p.data_ptr() + 4 * o:
+                raise RuntimeError("a LoRA parameter no longer lives in the ArenaAdamW parameter arena "
+                                   "(its .data was replaced); rebuild LoraGradArena and ArenaAdamW")
+
+    @torch.no_grad()
+    def step(self):
+        """Call after `arena.finish()`.  Clips (if max_grad_norm was given) and updates in place."""
+        from . import _native as nat
+        self._check_homes()
+        dev = self.arena.device
+        with torch.cuda.device(dev):
+            rc = nat.lib().b200lora_arena_adamw(
+                nat.ptr(self.flat_p), nat.ptr(self.arena.flat), nat.ptr(self.exp_avg), nat.ptr(self.exp_avg_sq),
+                self.flat_p.numel(), self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                self.max_grad_norm if self.max_grad_norm is not None else 0.0, nat.ptr(self.scratch),
+                nat.stream_ptr(dev))
+        nat.check(rc, "b200lora_arena_adamw")
+        # the kernel wrote through raw pointers: tell autograd's version counters, which key the
+        # per-layer LoRA pack caches (ops.BaseWeightCache.lora_pack, fused.SiblingGroup.pack)
+        for p in self.arena.params:
+            torch.autograd.graph.increment_version(p)
+
+    def grad_norm(self):
+        """L2 norm of the gradients seen by the last step (before clipping), as a device tensor."""
+        return self.scratch[0].sqrt()
+
+    def zero_grad(self, set_to_none: bool = False):
+        self.arena.zero()
+
+    def state_dict(self):
+        return {"exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "step": self.scratch[1:2],
+                "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay,
+                "max_grad_norm": self.max_grad_norm}
+
+    def load_state_dict(self, sd):
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        self.scratch[1:2].copy_(sd["step"])
+        for k in ("lr", "betas", "eps", "weight_decay", "max_grad_norm"):
+            if k in sd:
+                setattr(self, k, sd[k])

@@ -215,6 +215,20 @@ int b200lora_lora_grads_fused(const void* const* dY, const int64_t* ld_dy, int n
                               const int* r_each, int io_dtype, b200lora_stream_t stream);
 
 /*
+ * Optimizer step over the flat arenas — replaces clip_grad_norm_ + AdamW.step() over the
+ * LoRA parameters (train_lora_dreambooth.py:676, 878-888; cli_lora_pti.py:448-451) when parameters,
+ * gradients and both moments are contiguous fp32 arrays of n elements in the same order
+ * (dp.LoraGradArena + dp.ArenaAdamW).  max_grad_norm <= 0 disables the global-norm clip; otherwise
+ * grads are scaled in place by min(1, max_grad_norm / (||g|| + 1e-6)) as clip_grad_norm_ does.
+ * scratch: 2 floats on the device owned by the caller — [0] norm accumulator (reset here every call),
+ * [1] the step count t (initialise to 0; advanced here), kept on the device so the step can be captured
+ * in a CUDA graph.  Three stream operations (memset, norm, update); counts as one C-ABI call.
+ */
+int b200lora_arena_adamw(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                         float lr, float beta1, float beta2, float eps, float weight_decay,
+                         float max_grad_norm, float* scratch, b200lora_stream_t stream);
+
+/*
  * Weight merge — replaces lora.py:423  `weight + alpha * (up @ down).type(weight.dtype)`
  * (cli_lora_add.py:78 runs it on the CPU).  Wout may alias Win (in-place).
  * up [N,r], down [r,K] in lora_dtype; W in w_dtype.  Rounding follows the reference:

@@ -253,3 +253,58 @@ def test_graphed_training_step_equals_eager():
     for pe, pg in zip(ue.parameters(), ug.parameters()):
         if pe.requires_grad:      # Adam normalises: a gradient whose sign is rounding noise moves a weight by +-lr
             assert rel_err(pg, pe) < 0.15
+
+
+@pytest.mark.parametrize("max_norm", [None, 0.05])
+def test_arena_adamw_matches_torch_clip_and_adamw(max_norm):
+    """dp.ArenaAdamW (global-norm clip + AdamW over the flat arenas, b200lora_arena_adamw) against
+    torch.nn.utils.clip_grad_norm_ + torch.optim.AdamW on the same gradients, five steps."""
+    import copy
+    import itertools
+    from diffusion_finetuning_b200 import dp
+
+    class CrossAttention(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.to_q = torch.nn.Linear(64, 96, bias=False)
+            self.to_v = torch.nn.Linear(64, 72, bias=True)
+
+        def forward(self, x):
+            return self.to_q(x).sum(-1, keepdim=True) + self.to_v(x).mean(-1, keepdim=True)
+
+    torch.manual_seed(0)
+    base = CrossAttention().to(DEV)
+    base.requires_grad_(False)
+    models = []
+    for _ in range(2):
+        m = copy.deepcopy(base)
+        torch.manual_seed(1)
+        params, _ = L.inject_trainable_lora(m, {"CrossAttention"}, r=4)
+        with torch.no_grad():
+            for mod in m.modules():
+                if isinstance(mod, L.LoraInjectedLinear):
+                    mod.lora_up.weight.normal_(0, 0.02, generator=torch.Generator(DEV).manual_seed(2))
+        models.append((m, list(itertools.chain(*params))))
+    (ma, pa), (mb, pb) = models
+    arena_a, arena_b = dp.LoraGradArena(ma), dp.LoraGradArena(mb)
+    opt_a = dp.ArenaAdamW(arena_a, lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, max_grad_norm=max_norm)
+    opt_b = torch.optim.AdamW(pb, lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2)
+    names_a = dict(ma.named_parameters())
+    g = torch.Generator(DEV).manual_seed(5)
+    for step in range(5):
+        x = torch.randn(4, 50, 64, device=DEV, generator=g)
+        for m, arena in ((ma, arena_a), (mb, arena_b)):
+            arena.zero()
+            m(x).square().mean().backward()
+            arena.finish()
+        opt_a.step()
+        if max_norm is not None:
+            torch.nn.utils.clip_grad_norm_(pb, max_norm)
+        opt_b.step()
+        for k, p in mb.named_parameters():
+            if p.requires_grad:
+                assert rel_err(names_a[k], p) < 2e-5, (step, k, rel_err(names_a[k], p))
+    assert float(opt_a.scratch[1]) == 5.0
+    # the version bump reached the pack caches: a forward after the step sees the new weights
+    x = torch.randn(2, 8, 64, device=DEV, generator=g)
+    assert rel_err(ma(x), mb(x)) < 1e-4
