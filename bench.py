@@ -109,19 +109,53 @@ class ClockSampler:
 # live per-launch timing of the hot-path kernels (installed as ops.PROFILER)
 # ------------------------------------------------------------------------------------------------
 class LaunchProfiler:
-    def __init__(self):
+    """Eager mode: a fresh event pair around every launch.  `external=True`: the pairs are recorded while
+    the step is being CAPTURED (cudaEventRecordExternal -> event-record nodes of the graph), so every replay
+    re-stamps them and `harvest()` reads true device-side durations of the kernels inside the replayed step —
+    no host enqueue latency between the two stamps, which the eager pass cannot avoid when the host is the
+    slower side."""
+
+    def __init__(self, external=False):
         self.recs = []
         self.cur = None
+        self.external = external
+        self.pairs = []          # external mode: (kind, M, K, N, r, esize, a, b), stamped by each replay
+        self.acc = []            # external mode: accumulated ms per pair
+        self.replays = 0
+
+    def _event(self):
+        return torch.cuda.Event(enable_timing=True, external=True) if self.external \
+            else torch.cuda.Event(enable_timing=True)
 
     def begin(self, kind, M, K, N, r, esize):
-        a = torch.cuda.Event(enable_timing=True)
+        a = self._event()
         a.record()
         self.cur = (kind, M, K, N, r, esize, a)
 
     def end(self):
-        b = torch.cuda.Event(enable_timing=True)
+        b = self._event()
         b.record()
-        self.recs.append(self.cur + (b,))
+        (self.pairs if self.external else self.recs).append(self.cur + (b,))
+
+    def reset_capture(self):
+        """Forget the pairs recorded by eager warm-up steps; the next pass (the capture) defines them."""
+        self.pairs, self.acc, self.recs, self.replays = [], [], [], 0
+
+    def harvest(self):
+        """After a replay has finished (device synchronised): fold this replay's durations in."""
+        if not self.acc:
+            self.acc = [0.0] * len(self.pairs)
+        for i, rec in enumerate(self.pairs):
+            self.acc[i] += rec[6].elapsed_time(rec[7])
+        self.replays += 1
+
+    def _iter_ms(self):
+        if self.external:
+            for rec, ms in zip(self.pairs, self.acc):
+                yield rec[:6], ms, self.replays
+        else:
+            for rec in self.recs:
+                yield rec[:6], rec[6].elapsed_time(rec[7]), 1
 
     @staticmethod
     def work(kind, M, K, N, r, e):
@@ -136,24 +170,23 @@ class LaunchProfiler:
 
     def summary(self):
         out = {}
-        for kind, M, K, N, r, e, a, b in self.recs:
-            ms = a.elapsed_time(b)
+        for (kind, M, K, N, r, e), ms, n in self._iter_ms():
             fl, by = self.work(kind, M, K, N, r, e)
             s = out.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
-            s["launches"] += 1
+            s["launches"] += n
             s["ms"] += ms
-            s["flops"] += fl
-            s["bytes"] += by
+            s["flops"] += fl * n
+            s["bytes"] += by * n
         return out
 
     def by_shape(self, peak_tf, peak_gbs):
         """Per (kind, M, K, N, r): launches, mean event-bracketed duration, achieved TFLOP/s and GB/s."""
         acc = {}
-        for kind, M, K, N, r, e, a, b in self.recs:
+        for (kind, M, K, N, r, e), ms, n in self._iter_ms():
             fl, by = self.work(kind, M, K, N, r, e)
             s = acc.setdefault((kind, M, K, N, r), [0, 0.0, fl, by])
-            s[0] += 1
-            s[1] += a.elapsed_time(b)
+            s[0] += n
+            s[1] += ms
         rows = []
         for (kind, M, K, N, r), (n, ms, fl, by) in sorted(acc.items(), key=lambda kv: -kv[1][1]):
             us = ms * 1e3 / n
@@ -443,6 +476,8 @@ def main():
                     help="run q/k/v LoRA layers one launch each instead of fused per attention block")
     ap.add_argument("--memory-format", default="nchw", choices=["nchw", "channels_last"],
                     help="memory format of the frozen stock-PyTorch UNet (the reference scripts use nchw)")
+    ap.add_argument("--eager-profile", action="store_true",
+                    help="time our launches in eager steps (event pair per launch) instead of inside the replayed graph")
     ap.add_argument("--breakdown", default=None, help="write the per-kernel breakdown JSON here")
     args = ap.parse_args()
     if args.config == 3 and args.rank == 4:
@@ -525,9 +560,36 @@ def main():
     t_e2e = timed(lambda i: tr.step_from_host(host_pool[i % 4]), args.steps, dist_on, device)
     # ---- region 3: the same K steps with CUDA events around every launch of our kernels (roofline);
     # kept out of region 1 because an event between two launches defeats their programmatic overlap ----
-    ops.PROFILER = prof
-    t_prof = timed(lambda i: tr.eager_step(pool[i % 4]), args.steps, dist_on, device)
-    ops.PROFILER = None
+    timing_mode = "eager steps, one CUDA-event pair per launch"
+    t_prof = None
+    if tr.graphed is not None and not args.eager_profile and not dist_on:   # N>1 keeps the eager pass (no second NCCL capture)
+        # the step captured a second time WITH external event-record nodes around our launches: each replay
+        # stamps them on the device, so the durations are those of the kernels inside the replayed step
+        from diffusion_finetuning_b200 import dp
+        gprof = LaunchProfiler(external=True)
+        try:
+            ops.PROFILER = gprof
+            pg = dp.GraphedStep(tr.eager_step, pool[0], warmup=1, before_capture=gprof.reset_capture)
+            ops.PROFILER = None
+            pg(pool[0])
+            torch.cuda.synchronize(device)
+            t_prof = 0.0
+            for i in range(args.steps):
+                t_prof += timed(lambda _: pg(pool[i % 4]), 1, dist_on, device)
+                gprof.harvest()
+            prof = gprof
+            timing_mode = "external CUDA-event nodes inside the replayed step graph"
+            del pg
+        except Exception as exc:
+            ops.PROFILER = None
+            t_prof = None
+            print(f"[bench] in-graph launch timing unavailable ({type(exc).__name__}: {exc}); "
+                  "timing eager launches instead", file=sys.stderr)
+            torch.cuda.synchronize(device)
+    if t_prof is None:
+        ops.PROFILER = prof
+        t_prof = timed(lambda i: tr.eager_step(pool[i % 4]), args.steps, dist_on, device)
+        ops.PROFILER = None
     clk = clocks.stop() if rank == 0 else None
 
     # All ranks are done with the GPU.  Drop the captured graph (it holds NCCL work) and leave through
@@ -554,7 +616,7 @@ def main():
                 "launches_per_step": gemm["launches"] / args.steps,
                 "avg_launch_us": gemm["ms"] * 1e3 / max(1, gemm["launches"]),
                 "share_of_step": gemm["ms"] / args.steps / step_ms,
-                "profiled_ms_per_step": step_ms,
+                "profiled_ms_per_step": step_ms, "launch_timing": timing_mode,
                 "achieved_hbm_gbs": gemm["bytes"] / (gemm["ms"] * 1e-3) / 1e9 if gemm["ms"] else 0.0}
     if "grads" in summ:
         s = summ["grads"]

@@ -261,7 +261,7 @@ class GraphedStep:
     updates invalidated them, so every replay re-packs from the live parameters.
     """
 
-    def __init__(self, step_fn, example_batch: dict, warmup: int = 3):
+    def __init__(self, step_fn, example_batch: dict, warmup: int = 3, before_capture=None):
         dev = next(iter(example_batch.values())).device
         self.static = {k: v.clone() for k, v in example_batch.items()}
         side = torch.cuda.Stream(device=dev)
@@ -273,6 +273,8 @@ class GraphedStep:
         torch.cuda.synchronize(dev)
         from . import _native as nat
         self.graph = torch.cuda.CUDAGraph()
+        if before_capture is not None:      # e.g. a launch profiler dropping what the warm-up steps recorded
+            before_capture()
         n0 = nat.LAUNCHES
         with torch.cuda.graph(self.graph):
             self.loss = step_fn(self.static)
