@@ -68,6 +68,10 @@ cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, i
                                 cudaStream_t);
 cudaError_t launch_arena_adamw(float*, float*, float*, float*, long long, float, float, float, float, float,
                                float, float*, cudaStream_t);
+cudaError_t launch_ti_grad_rows(const void*, const long long*, long long, int, const long long*, int, float*, int,
+                                cudaStream_t);
+cudaError_t launch_ti_step(void*, int, int, const long long*, int, float*, const float*, float*, float*, float,
+                           float, float, float, float, float, float, float, float*, cudaStream_t);
 
 // ---------------------------------------------------------------------------------------
 // device info
@@ -777,6 +781,36 @@ extern "C" int b200lora_arena_adamw(float* params, float* grads, float* exp_avg,
   cudaError_t e = launch_arena_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
                                      max_grad_norm, scratch, reinterpret_cast<cudaStream_t>(stream_));
   if (e != cudaSuccess) { set_error("arena_adamw launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_ti_grad_rows(const void* dY, const int64_t* token_ids, int64_t n_tokens, int D,
+                                     const int64_t* rows, int P, float* grad_rows, int io_dtype,
+                                     b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!dY || !token_ids || !rows || !grad_rows) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (D < 1 || P < 1 || P > 65535 || n_tokens < 0) { set_error("ti_grad_rows: bad shape (D=%d, P=%d)", D, P); return B200LORA_E_SHAPE; }
+  if (n_tokens == 0) return 0;
+  cudaError_t e = launch_ti_grad_rows(dY, reinterpret_cast<const long long*>(token_ids), n_tokens, D,
+                                      reinterpret_cast<const long long*>(rows), P, grad_rows, io_dtype,
+                                      reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("ti_grad_rows launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_ti_step(void* table, int table_dtype, int D, const int64_t* rows, int P, float* master_rows,
+                                const float* grad_rows, float* exp_avg, float* exp_avg_sq, int step, float lr,
+                                float beta1, float beta2, float eps, float weight_decay, float lambda_,
+                                float target_norm, float* norms_out, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!table || !rows || !master_rows || !grad_rows || !exp_avg || !exp_avg_sq) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(table_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (D < 1 || P < 1 || step < 1) { set_error("ti_step: bad shape or step (D=%d, P=%d, step=%d)", D, P, step); return B200LORA_E_SHAPE; }
+  cudaError_t e = launch_ti_step(table, table_dtype, D, reinterpret_cast<const long long*>(rows), P, master_rows,
+                                 grad_rows, exp_avg, exp_avg_sq, (float)step, lr, beta1, beta2, eps, weight_decay,
+                                 lambda_, target_norm, norms_out, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("ti_step launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

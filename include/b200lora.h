@@ -229,6 +229,32 @@ int b200lora_arena_adamw(float* params, float* grads, float* exp_avg, float* exp
                          float max_grad_norm, float* scratch, b200lora_stream_t stream);
 
 /*
+ * Textual-inversion step — replaces, for the placeholder-token rows of the CLIP token
+ * embedding, cli_lora_pti.py:309-346: the dense embedding gradient + dense AdamW over [vocab, D]
+ * (cli_lora_pti.py:651-657), the norm decay of the placeholder rows (:317-335) and the restore of every
+ * other row from a clone of the table (:280, :344-346).  Only P rows ever change, so only P rows are touched.
+ *   b200lora_ti_grad_rows  grad_rows[p, :] += sum over tokens t with token_ids[t] == rows[p] of dY[t, :]
+ *                          dY [n_tokens, D] in io_dtype (gradient of the embedding OUTPUT), token_ids [n_tokens]
+ *                          int64, rows [P] int64 (placeholder token ids), grad_rows [P, D] fp32 (ADDED into;
+ *                          tokens are summed in index order: bit-reproducible).
+ *   b200lora_ti_step       AdamW (torch.optim.AdamW semantics: decoupled decay, bias correction with `step`
+ *                          >= 1, eps outside the corrected sqrt) on master_rows [P, D] fp32 with moments
+ *                          exp_avg / exp_avg_sq [P, D]; then, when lambda_ >= 0,
+ *                          w <- w / max(|w|, 1e-12) * (|w| + lambda_ * (target_norm - |w|))
+ *                          (lambda_ = min(1, 100 * lr), target_norm = 0.4 in the reference; lambda_ < 0 skips
+ *                          the decay = clip_ti_decay False); then table[rows[p], :] = master_rows[p, :] cast to
+ *                          table_dtype.  norms_out (nullable) [2, P] fp32: row norms before and after the decay
+ *                          (the reference prints both).
+ */
+int b200lora_ti_grad_rows(const void* dY, const int64_t* token_ids, int64_t n_tokens, int D,
+                          const int64_t* rows, int P, float* grad_rows, int io_dtype,
+                          b200lora_stream_t stream);
+int b200lora_ti_step(void* table, int table_dtype, int D, const int64_t* rows, int P, float* master_rows,
+                     const float* grad_rows, float* exp_avg, float* exp_avg_sq, int step, float lr,
+                     float beta1, float beta2, float eps, float weight_decay, float lambda_,
+                     float target_norm, float* norms_out, b200lora_stream_t stream);
+
+/*
  * Weight merge — replaces lora.py:423  `weight + alpha * (up @ down).type(weight.dtype)`
  * (cli_lora_add.py:78 runs it on the CPU).  Wout may alias Win (in-place).
  * up [N,r], down [r,K] in lora_dtype; W in w_dtype.  Rounding follows the reference:

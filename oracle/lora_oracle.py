@@ -181,3 +181,28 @@ def safeloras_layout(names_ranks_targets):
             meta[f"{name}:{i}:rank"] = str(r)
             keys += [f"{name}:{i}:up", f"{name}:{i}:down"]
     return sorted(keys), meta
+
+
+# ---------------------------------------------------------------------------------------------
+# textual-inversion step (cli_lora_pti.py) — restated; cli_lora_pti.py itself imports diffusers/fire/wandb
+# at module top and cannot be imported here, so the optimizer IS torch.optim.AdamW as at :651-657
+# ---------------------------------------------------------------------------------------------
+def ti_make_optimizer(embedding: nn.Embedding, lr, weight_decay=0.0):
+    """cli_lora_pti.py:651-657."""
+    return torch.optim.AdamW(embedding.parameters(), lr=lr, betas=(0.9, 0.999), eps=1e-08, weight_decay=weight_decay)
+
+
+@torch.no_grad()
+def ti_post_step(embedding: nn.Embedding, orig_embeds_params, index_no_updates, lr, clip_ti_decay=True):
+    """cli_lora_pti.py:315-346, after `optimizer.step(); optimizer.zero_grad()`: norm decay of the
+    placeholder rows with lambda = min(1, 100·lr), then every other row restored from the clone taken
+    before training (:280).  Returns (pre_norm, current_norm) as the reference prints them."""
+    index_updates = ~index_no_updates
+    w = embedding.weight
+    pre_norm = w[index_updates, :].norm(dim=-1, keepdim=True)
+    if clip_ti_decay:
+        lambda_ = min(1.0, 100 * lr)
+        w[index_updates] = F.normalize(w[index_updates, :], dim=-1) * (pre_norm + lambda_ * (0.4 - pre_norm))
+    current_norm = w[index_updates, :].norm(dim=-1)
+    w[index_no_updates] = orig_embeds_params[index_no_updates]
+    return pre_norm.squeeze(-1), current_norm
