@@ -41,6 +41,7 @@ SIGNATURES = {
                                    _i32, _i32, _vp, _i64, _vp]),
     "b200lora_lora_grads_workspace": (_i64, [_i64, _i32, _i32, _i32]),
     "b200lora_arena_adamw": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
+    "b200lora_flat_axpby": (_i32, [_vp, _vp, _vp, _i64, _f32, _f32, _i32, _i32, _vp]),
     "b200lora_ti_grad_rows": (_i32, [_vp, _vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp]),
     "b200lora_ti_step": (_i32, [_vp, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _f32, _f32, _f32, _f32, _f32,
                                 _f32, _f32, _vp, _vp]),

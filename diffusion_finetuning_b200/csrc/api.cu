@@ -68,6 +68,7 @@ cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, i
                                 cudaStream_t);
 cudaError_t launch_arena_adamw(float*, float*, float*, float*, long long, float, float, float, float, float,
                                float, float*, cudaStream_t);
+cudaError_t launch_flat_axpby(const void*, const void*, void*, long long, float, float, int, int, cudaStream_t);
 cudaError_t launch_ti_grad_rows(const void*, const long long*, long long, int, const long long*, int, float*, int,
                                 cudaStream_t);
 cudaError_t launch_ti_step(void*, int, int, const long long*, int, float*, const float*, float*, float*, float,
@@ -781,6 +782,18 @@ extern "C" int b200lora_arena_adamw(float* params, float* grads, float* exp_avg,
   cudaError_t e = launch_arena_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
                                      max_grad_norm, scratch, reinterpret_cast<cudaStream_t>(stream_));
   if (e != cudaSuccess) { set_error("arena_adamw launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_flat_axpby(const void* a, const void* b, void* out, int64_t n, float alpha, float beta,
+                                   int in_dtype, int out_dtype, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!a || !out) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(in_dtype) || !valid_dtype(out_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (n < 0) { set_error("flat_axpby: negative length"); return B200LORA_E_SHAPE; }
+  if (n == 0) return 0;
+  cudaError_t e = launch_flat_axpby(a, b, out, n, alpha, beta, in_dtype, out_dtype, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("flat_axpby launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

@@ -229,6 +229,18 @@ int b200lora_arena_adamw(float* params, float* grads, float* exp_avg, float* exp
                          float max_grad_norm, float* scratch, b200lora_stream_t stream);
 
 /*
+ * Flat pass over LoRA artefacts: out[i] = rnd(alpha·a[i]) (+ rnd(beta·b[i]), then rnd of the sum),
+ * every rounding to in_dtype as ATen's temporaries are, then converted to out_dtype.
+ *   b != NULL  replaces the `lpl` mix of two LoRA lists, cli_lora_add.py:49-58
+ *              (`alpha * x1.data + (1 - alpha) * x2.data`, bit-identical to the CPU result);
+ *   b == NULL  with alpha = 1 is the dtype conversion of a whole parameter arena for the `.pt` writer
+ *              (lora.py:201-213: `.to(torch.float16)` per tensor).
+ * a, b [n] in in_dtype, out [n] in out_dtype; out may alias a when the dtypes are equal.
+ */
+int b200lora_flat_axpby(const void* a, const void* b, void* out, int64_t n, float alpha, float beta,
+                        int in_dtype, int out_dtype, b200lora_stream_t stream);
+
+/*
  * Textual-inversion step — replaces, for the placeholder-token rows of the CLIP token
  * embedding, cli_lora_pti.py:309-346: the dense embedding gradient + dense AdamW over [vocab, D]
  * (cli_lora_pti.py:651-657), the norm decay of the placeholder rows (:317-335) and the restore of every
