@@ -183,6 +183,8 @@ class TrainConfig:
     use_cuda_graph: bool = False                 # replay fwd+bwd+exchange+clip+AdamW as one CUDA graph
     bucket_bytes: int = 1 << 20
     seed: Optional[int] = None
+    learning_rate_ti: Optional[float] = None     # continue_inversion_lr / ti_lr (cli_lora_pti.py:715-722)
+    clip_ti_decay: bool = False                  # perform_tuning has no norm decay; train_inversion has (:317)
 
 
 class LoraTrainer:
@@ -192,7 +194,10 @@ class LoraTrainer:
 
     def __init__(self, unet: nn.Module, cfg: TrainConfig, text_encoder: Optional[nn.Module] = None, vae=None,
                  noise_schedule: Optional[DDPMNoiseSchedule] = None, loss_fn: Optional[Callable] = None,
-                 extra_params: Iterable[nn.Parameter] = (), process_group=None):
+                 extra_params: Iterable[nn.Parameter] = (), process_group=None, placeholder_rows=None):
+        """`placeholder_rows` (ti.PlaceholderTokenRows, installed on the text encoder's token embedding): the
+        `continue_inversion` group of cli_lora_pti.py:713-728.  Its gradient rows ride in the arena (exchanged and
+        clipped with the LoRA gradients); its update is `ti.PlaceholderAdamW` right after the LoRA optimizer."""
         self.cfg, self.unet, self.text_encoder, self.vae = cfg, unet, text_encoder, vae
         self.noise = noise_schedule or DDPMNoiseSchedule()
         self._own_loss = loss_fn is None
@@ -223,12 +228,23 @@ class LoraTrainer:
         if extra:
             groups.append({"params": extra, "lr": cfg.learning_rate})
         holder = nn.ModuleList(models)          # a walk root for the arena; the models are not modified
-        self.arena = dp.LoraGradArena(holder, extra_params=extra, bucket_bytes=cfg.bucket_bytes,
+        self.ti_opt = None
+        arena_extra = list(extra)
+        if placeholder_rows is not None:
+            from . import ti
+            arena_extra.append(placeholder_rows.rows)
+            self.ti_opt = ti.PlaceholderAdamW(
+                placeholder_rows, lr=cfg.learning_rate if cfg.learning_rate_ti is None else cfg.learning_rate_ti,
+                betas=(cfg.adam_beta1, cfg.adam_beta2), eps=cfg.adam_epsilon, weight_decay=cfg.adam_weight_decay,
+                clip_ti_decay=cfg.clip_ti_decay)
+        self.arena = dp.LoraGradArena(holder, extra_params=arena_extra, bucket_bytes=cfg.bucket_bytes,
                                       process_group=process_group)
         self.arena.broadcast_params(0)
         self.device = self.arena.device
         on_cuda = self.device.type == "cuda"
-        self.graph_ok = bool(cfg.use_cuda_graph and on_cuda and cfg.gradient_accumulation_steps == 1)
+        # (the placeholder-row update takes lr and step as launch arguments: not replayable)
+        self.graph_ok = bool(cfg.use_cuda_graph and on_cuda and cfg.gradient_accumulation_steps == 1
+                             and self.ti_opt is None)
         opt_kw = dict(lr=cfg.learning_rate, betas=(cfg.adam_beta1, cfg.adam_beta2), weight_decay=cfg.adam_weight_decay,
                       eps=cfg.adam_epsilon)
         if on_cuda:
@@ -238,7 +254,10 @@ class LoraTrainer:
                 g["lr"] = torch.tensor(float(g["lr"]), dtype=torch.float32, device=self.device)
             opt_kw["lr"] = torch.tensor(float(cfg.learning_rate), dtype=torch.float32, device=self.device)
         self.optimizer = torch.optim.AdamW(groups, **opt_kw)
-        self.lr_scheduler = get_scheduler(cfg.lr_scheduler, self.optimizer, cfg.lr_warmup_steps, cfg.max_train_steps)
+        sched_target = self.optimizer
+        if self.ti_opt is not None:             # one schedule over every group, as lr_scheduler_lora (:746-751)
+            sched_target = argparse.Namespace(param_groups=self.optimizer.param_groups + self.ti_opt.param_groups)
+        self.lr_scheduler = get_scheduler(cfg.lr_scheduler, sched_target, cfg.lr_warmup_steps, cfg.max_train_steps)
         self.global_step = 0          # counts loop iterations, as the reference's does (:891)
         self.last_save = 0
         self._micro = 0
@@ -286,6 +305,8 @@ class LoraTrainer:
         if cfg.max_grad_norm is not None and cfg.max_grad_norm > 0:
             self.arena.clip_grad_norm_(cfg.max_grad_norm)
         self.optimizer.step()
+        if self.ti_opt is not None:
+            self.ti_opt.step()
 
     def _whole_step(self, b):
         self.arena.zero()

@@ -98,3 +98,80 @@ def test_cli_synthetic_job_writes_reference_artefacts(tmp_path):
     loras = torch.load(out / "lora_weight.pt")
     assert len(loras) % 2 == 0 and all(t.dtype == torch.float16 for t in loras)
     assert any(t.abs().sum() > 0 for t in loras[::2])            # lora_up left zero => nothing trained
+
+
+def test_config4_joint_unet_clip_and_placeholder_rows(tmp_path):
+    """BASELINE config 4 in small: UNet LoRA + CLIP text-encoder LoRA + placeholder-token rows in ONE
+    LoraTrainer (cli_lora_pti.perform_tuning with continue_inversion, :408-489, 699-751) against the same loop
+    in plain torch.  The reference's loop trains every embedding row that occurs in a prompt (dense gradient, no
+    restore in this phase); this package restricts training to the placeholder rows (ti.py), so the plain-torch
+    side zeroes the other rows' gradient before the clip and restores them after the step."""
+    from transformers import CLIPTextConfig, CLIPTextModel
+    from diffusion_finetuning_b200 import ti
+    V, rows = 200, [198, 199]
+    ccfg = CLIPTextConfig(vocab_size=V, hidden_size=32, intermediate_size=64, num_hidden_layers=2,
+                          num_attention_heads=4, max_position_embeddings=77)
+
+    def build():
+        unet, unet_params = _unet()
+        torch.manual_seed(5)
+        clip = CLIPTextModel(ccfg).to(DEV)
+        clip.requires_grad_(False)
+        torch.manual_seed(6)
+        clip_params, _ = L.inject_trainable_lora(clip, {"CLIPAttention"}, r=4)
+        g = torch.Generator().manual_seed(7)
+        with torch.no_grad():
+            for m in clip.modules():
+                if isinstance(m, L.LoraInjectedLinear):
+                    m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(DEV))
+        return unet, unet_params, clip, clip_params
+
+    g = torch.Generator().manual_seed(8)
+    data = []
+    for _ in range(4):
+        ids = torch.randint(0, V - 2, (2, 77), generator=g)
+        ids[:, 4], ids[:, 5] = rows[0], rows[1]
+        data.append({"latents": torch.randn(2, 4, 32, 32, generator=g).to(DEV), "input_ids": ids.to(DEV),
+                     "noise": torch.randn(2, 4, 32, 32, generator=g).to(DEV),
+                     "timesteps": torch.randint(0, 1000, (2,), generator=g).to(DEV)})
+    kw = dict(learning_rate=1e-3, learning_rate_text=5e-4, learning_rate_ti=2e-3, lr_scheduler="linear",
+              lr_warmup_steps=0, max_train_steps=4, max_grad_norm=1.0, train_text_encoder=True, scheduler_first=True)
+    unet, _, clip, _ = build()
+    emb = clip.get_input_embeddings()
+    table0 = emb.weight.detach().clone()
+    pr = ti.PlaceholderTokenRows(emb, rows).install()
+    tr = T.LoraTrainer(unet, _cfg(tmp_path, **kw), text_encoder=clip, placeholder_rows=pr)
+    assert not tr.graph_ok and len(tr.lr_scheduler.get_last_lr()) == 3
+    losses = [tr.train_step(b).item() for b in data]
+
+    r_unet, r_up, r_clip, r_cp = build()
+    r_emb = r_clip.get_input_embeddings()
+    r_emb.weight.requires_grad_(True)
+    orig = r_emb.weight.detach().clone()
+    keep = torch.ones(V, dtype=torch.bool, device=DEV)
+    keep[rows] = False
+    opt = torch.optim.AdamW([{"params": itertools.chain(*r_up), "lr": 1e-3}, {"params": itertools.chain(*r_cp), "lr": 5e-4},
+                             {"params": [r_emb.weight], "lr": 2e-3}], weight_decay=1e-2)
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, T._schedule_factor("linear", 0, 4))
+    ns = T.DDPMNoiseSchedule()
+    ref_losses = []
+    for b in data:
+        sched.step()                                       # cli_lora_pti.py:434
+        opt.zero_grad()
+        noisy = ns.add_noise(b["latents"], b["noise"], b["timesteps"])
+        pred = r_unet(noisy, b["timesteps"], r_clip(b["input_ids"])[0])
+        loss = torch.nn.functional.mse_loss(pred.float(), b["noise"].float(), reduction="mean")
+        loss.backward()
+        r_emb.weight.grad[keep] = 0
+        torch.nn.utils.clip_grad_norm_(itertools.chain(r_unet.parameters(), r_clip.parameters()), 1.0)   # :448-450
+        opt.step()
+        with torch.no_grad():
+            r_emb.weight[keep] = orig[keep]
+        ref_losses.append(loss.item())
+    assert losses == pytest.approx(ref_losses, rel=5e-4)
+    for a, b in zip(_state(unet) + _state(clip), _state(r_unet) + _state(r_clip)):
+        assert rel_err(a, b) < 3e-3
+    assert rel_err(emb.weight[rows], r_emb.weight[rows]) < 1e-4
+    assert rel_err(emb.weight[rows] - table0[rows], r_emb.weight[rows] - orig[rows]) < 2e-2      # the UPDATE agrees
+    assert torch.equal(emb.weight[keep], table0[keep])
+    assert tr.lr_scheduler.get_last_lr() == pytest.approx(sched.get_last_lr())
