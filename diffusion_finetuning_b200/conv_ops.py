@@ -37,6 +37,7 @@ class _ConvState:
 
     def __init__(self):
         self.store = {}
+        self.grad_on = True        # grad mode at apply time (set by lora_conv2d; needs_input_grad ignores it)
 
     @staticmethod
     def key(t):
@@ -60,12 +61,14 @@ class _ConvState:
         self.store.pop(("pack", cdt), None)      # the backward operand carries LoRA columns: re-pack
         return out
 
-    def pack(self, A, B, bias, w, cdt, need_bwd):
+    def pack(self, A, B, bias, w, cdt, need_bwd, live=False):
         """(A_pack [16,R*S*Cp], Bn_pack [Cout,64], Wb or None); Wb's LoRA columns refreshed here."""
         k = ("pack", cdt)
         key = (self.key(A), self.key(B), None if bias is None else self.key(bias), self.key(w), need_bwd)
         hit = self.store.get(k)
-        if hit is not None and hit[0] == key:
+        if live:                                # being trained: never cached (ops.BaseWeightCache.lora_pack)
+            self.store.pop(k, None)
+        elif hit is not None and hit[0] == key:
             return hit[1]
         Cout, Cin, R, S = w.shape
         r = A.shape[0]
@@ -81,7 +84,8 @@ class _ConvState:
                 Cout, Cin, R, S, r, nat.dtype_code(cdt), nat.stream_ptr(w.device))
         nat.check(rc, "b200lora_conv2d_pack_lora")
         out = (a_pack, bn_pack, wb)
-        self.store[k] = (key, out)
+        if not live:
+            self.store[k] = (key, out)
         return out
 
     def zeros(self, n, cdt, device):
@@ -122,10 +126,11 @@ class _LoraConv2dFn(torch.autograd.Function):
             raise nat.B200LoraError(f"LoraInjectedConv2d: channel counts must be multiples of 8 (got {Cin}, {Cout})")
         if r > 16:
             raise nat.B200LoraError("LoraInjectedConv2d: the tcgen05 path supports r <= 16")
-        need_grad = any(ctx.needs_input_grad[i] for i in (0, 3, 4))
+        need_grad = state.grad_on and any(ctx.needs_input_grad[i] for i in (0, 3, 4))
         xh = _nhwc(x, cdt)
         wk = state.base(w0, cdt, 0)
-        a_pack, bn_pack, wb = state.pack(A, B, bias, w0, cdt, need_grad and geo[2] == 1 and geo[3] == 1)
+        a_pack, bn_pack, wb = state.pack(A, B, bias, w0, cdt, need_grad and geo[2] == 1 and geo[3] == 1,
+                                         live=state.grad_on and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]))
         M_in = xh.shape[0]
         T = None
         if need_grad:
@@ -215,5 +220,6 @@ def lora_conv2d(module, x):
     state = getattr(module, "_conv_state", None)
     if state is None:
         state = module._conv_state = _ConvState()
+    state.grad_on = torch.is_grad_enabled()
     return _LoraConv2dFn.apply(x, conv.weight, conv.bias, A, module.lora_up.weight, module.scale,
                                (kh, kw, sh, sw, ph, pw, dh, dw), state)

@@ -44,6 +44,7 @@ class SiblingGroup:
         self.layers = list(layers)
         self.pending = None
         self.wasted = 0
+        self.grad_on = True         # grad mode at apply time (member_forward)
         self.enabled = True
         self.fused_calls = 0
         self._store = {}
@@ -89,13 +90,15 @@ class SiblingGroup:
         self._store[slot] = (key, out)
         return out
 
-    def pack(self, cdt):
+    def pack(self, cdt, live=False):
         """(pack buffer, A_cat, B_bd, bias_cat): b200lora_pack_lora over the concatenated factors."""
         Ls = self.layers
         key = tuple((_key(m.lora_down.weight), _key(m.lora_up.weight), float(m.scale),
                      None if m.linear.bias is None else _key(m.linear.bias)) for m in Ls) + (cdt,)
         hit = self._store.get("pack")
-        if hit is not None and hit[0] == key:
+        if live:                                # being trained: never cached (ops.BaseWeightCache.lora_pack)
+            self._store.pop("pack", None)
+        elif hit is not None and hit[0] == key:
             return hit[1]
         N, K = Ls[0].linear.weight.shape
         dev = Ls[0].linear.weight.device
@@ -121,7 +124,8 @@ class SiblingGroup:
                                                   nat.stream_ptr(dev))
             nat.check(rc, "b200lora_pack_lora(fused)")
         out = (buf, A_cat, B_bd, bias_cat)
-        self._store["pack"] = (key, out)
+        if not live:
+            self._store["pack"] = (key, out)
         return out
 
     # ---- the hook ----
@@ -148,6 +152,7 @@ class SiblingGroup:
         flat = []
         for m in self.layers:
             flat += [m.lora_down.weight, m.lora_up.weight]
+        self.grad_on = torch.is_grad_enabled()      # needs_input_grad inside the Function ignores the grad mode
         outs = list(_FusedSiblingFn.apply(x, self, *flat))
         self.fused_calls += 1
         y = outs[idx]
@@ -182,9 +187,9 @@ class _FusedSiblingFn(torch.autograd.Function):
             x2 = x2.to(cdt)
         x2 = x2.contiguous()
         M = x2.shape[0]
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = group.grad_on and any(ctx.needs_input_grad)
         w = group.w_cat(cdt, False)
-        pack, A_cat, B_bd, bias_cat = group.pack(cdt)
+        pack, A_cat, B_bd, bias_cat = group.pack(cdt, live=group.grad_on and any(ctx.needs_input_grad[2:]))
         y = torch.empty((M, Ncat), dtype=cdt, device=x.device)
         T = torch.empty((M, r_total), dtype=cdt, device=x.device) if need_grad else None
         if M > 0:

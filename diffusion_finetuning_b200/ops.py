@@ -53,15 +53,22 @@ class BaseWeightCache:
         self._store[slot] = (key, out)
         return out
 
-    def lora_pack(self, A, B, bias, dtype):
+    def lora_pack(self, A, B, bias, dtype, live=False):
         """The packed LoRA operands of the tcgen05 kernel (b200lora_pack_lora): one buffer of
         80·(K+N) elements in `dtype` holding the rank rows and tail blocks of forward and backward
-        (and the frozen bias, which the forward adds through the tail MMA).  Re-packed (one tiny
-        launch, fresh buffer) whenever either factor changes: optimizer steps bump `_version`,
-        monkeypatch_* swap the Parameter."""
+        (and the frozen bias, which the forward adds through the tail MMA).
+
+        `live` = the factors are being TRAINED (the caller's autograd node needs their gradient): the pack
+        is rebuilt on every call and never cached: fused/capturable optimizers (`torch.optim.AdamW(fused=True)`) update
+        parameters without bumping `_version`, so no key can tell that a step happened.  One tiny launch
+        per layer per step; inside a captured step it is part of the graph.  Otherwise (inference) the
+        pack is cached and re-built when a factor changes: `monkeypatch_*` swap the Parameter, in-place
+        autograd-visible edits bump `_version`."""
         key = (self._key(A), self._key(B), None if bias is None else self._key(bias), dtype)
         hit = self._store.get("pack")
-        if hit is not None and hit[0] == key:
+        if live:
+            self._store.pop("pack", None)     # whatever was cached predates the coming optimizer steps
+        elif hit is not None and hit[0] == key:
             return hit[1]
         r, K = A.shape
         N = B.shape[0]
@@ -74,7 +81,8 @@ class BaseWeightCache:
                                               nat.ptr(buf), K, N, r, nat.dtype_code(dtype),
                                               nat.stream_ptr(A.device))
         nat.check(rc, "b200lora_pack_lora")
-        self._store["pack"] = (key, buf)
+        if not live:
+            self._store["pack"] = (key, buf)
         return buf
 
     def invalidate(self):
@@ -152,7 +160,7 @@ class _LoraLinearFn(torch.autograd.Function):
     """y = x·W0ᵀ + b + s·(x·Aᵀ)·Bᵀ as ONE kernel; backward = fused dX kernel + token reductions."""
 
     @staticmethod
-    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic, sink=None):
+    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic, sink=None, grad_on=True):
         nat.require_cuda(x, "LoraInjectedLinear.forward")
         for name, t in (("linear.weight", w0), ("lora_down.weight", A), ("lora_up.weight", B)):
             if t.device != x.device:
@@ -181,12 +189,13 @@ class _LoraLinearFn(torch.autograd.Function):
         Bc = B.detach().contiguous()
         bc = bias.detach().contiguous() if bias is not None else None
         use_tc = _tc_ok(cdt, K, N, r, x.device, impl)
-        need_grad = any(ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
+        # needs_input_grad reflects requires_grad only; `grad_on` is the grad mode at apply time
+        need_grad = grad_on and any(ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
         y = torch.empty((M, N), dtype=cdt, device=x.device)
         T = torch.empty((M, r), dtype=cdt, device=x.device) if need_grad else None
         pack = None
         if use_tc and M > 0:
-            pack = cache.lora_pack(A, B, bias, cdt)
+            pack = cache.lora_pack(A, B, bias, cdt, live=grad_on and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]))
         if M > 0:
             with torch.cuda.device(x.device), _Prof("fwd", M, K, N, r, x2.element_size()):
                 rc = lib.b200lora_linear_fwd(
@@ -280,7 +289,7 @@ class _LoraLinearFn(torch.autograd.Function):
                 dx = dx.to(x_dtype)
         else:
             dx = None
-        return dx, dW, db, dA, dB, None, None, None, None, None
+        return dx, dW, db, dA, dB, None, None, None, None, None, None
 
 
 def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None,
@@ -292,7 +301,7 @@ def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, d
     if deterministic is None:
         deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
     return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic,
-                               sink)
+                               sink, torch.is_grad_enabled())
 
 
 # --------------------------------------------------------------------------------------------
