@@ -45,6 +45,8 @@ cudaError_t launch_conv_zcat_tc(const CUtensorMap*, const CUtensorMap*, const vo
                                 long long, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
                         int, int, int, int, cudaStream_t);
+cudaError_t launch_pack_seg(const void* const*, const void* const*, const void* const*, const float*, const int*,
+                            int, int, int, void*, void*, void*, void*, int, int, int, cudaStream_t);
 template <typename TIO>
 cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
                         const void*, long long, long long, const void*, long long, long long, int,
@@ -441,6 +443,38 @@ extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, co
   cudaError_t e = launch_pack(A, B, ab_dtype, bias, bias_dtype, A_pack, Bt_pack, Bn_pack, At_pack, K,
                               N, r, io_dtype, stream);
   if (e != cudaSuccess) { set_error("pack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int b200lora_pack_lora_fused(const void* const* A, const void* const* B, const void* const* bias,
+                                        const float* scales, const int* r_each, int nseg, int ab_dtype,
+                                        int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                                        b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!A || !B || !scales || !r_each || !pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (nseg < 1 || nseg > 4) { set_error("pack_lora_fused: 1 <= nseg <= 4"); return B200LORA_E_SHAPE; }
+  if (!valid_dtype(ab_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
+    set_error("pack_lora_fused: io dtype must be bf16/fp16"); return B200LORA_E_DTYPE;
+  }
+  int r_total = 0;
+  bool any_bias = false;
+  for (int s = 0; s < nseg; ++s) {
+    if (!A[s] || !B[s] || r_each[s] < 1) { set_error("pack_lora_fused: segment %d has a null factor or r < 1", s); return B200LORA_E_ARG; }
+    r_total += r_each[s];
+    any_bias |= bias && bias[s];
+  }
+  if (any_bias && !valid_dtype(bias_dtype)) { set_error("bad bias dtype enum"); return B200LORA_E_DTYPE; }
+  if (K < 1 || Nseg < 1 || r_total > 16) {
+    set_error("pack_lora_fused: needs K, Nseg >= 1 and sum of ranks <= 16, got %d", r_total); return B200LORA_E_SHAPE;
+  }
+  if (!aligned16(pack)) { set_error("pack_lora_fused: pack buffer must be 16-byte aligned"); return B200LORA_E_ALIGN; }
+  const int64_t N = (int64_t)nseg * Nseg;
+  char* base = reinterpret_cast<char*>(pack);
+  cudaError_t e = launch_pack_seg(A, B, bias, scales, r_each, nseg, ab_dtype, bias_dtype, base,
+                                  base + 2ll * 16 * K, base + 2ll * 16 * (K + N),
+                                  base + 2ll * (16 * (K + N) + 64ll * N), K, Nseg, io_dtype,
+                                  reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("pack_lora_fused launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

@@ -242,4 +242,97 @@ cudaError_t launch_pack(const void* A, const void* B, int ab_dtype, const void* 
   return cudaGetLastError();
 }
 
+// ---- segmented pack: the pack of up to 4 sibling layers' CONCATENATED problem (fused q/k/v), written
+// straight from the layers' own factors: A_cat = [A_0; A_1; ...] (r_total rows), B block-diagonal with each
+// layer's scale folded in, bias concatenated.  Replaces cat / zeros / slice-assign / mul launches per group.
+struct PackSegs {
+  const void* A[4];
+  const void* B[4];
+  const void* bias[4];
+  float scale[4];
+  int r[4];
+  int off[4];
+  int nseg;
+};
+
+template <typename TIO>
+__global__ void lora_pack_seg_kernel(const PackSegs sg, int ab_dtype, int bias_dtype, TIO* __restrict__ A_pack,
+                                     TIO* __restrict__ Bt_pack, TIO* __restrict__ Bn_pack,
+                                     TIO* __restrict__ At_pack, int K, int Nseg, int r_total) {
+  const int N = sg.nseg * Nseg;
+  const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
+  auto seg_of_rank = [&](int j) {
+    int s = 0;
+#pragma unroll
+    for (int q = 1; q < 4; ++q)
+      if (q < sg.nseg && j >= sg.off[q]) s = q;
+    return s;
+  };
+  auto a_val = [&](int j, int k) -> float {
+    if (j >= r_total) return 0.f;
+    const int s = seg_of_rank(j);
+    return load_as_float(sg.A[s], ab_dtype, (long long)(j - sg.off[s]) * K + k);
+  };
+  auto b_val = [&](int n, int j) -> float {      // block-diagonal, scale folded (rounded once, to TIO)
+    if (j >= r_total) return 0.f;
+    const int s = n / Nseg;
+    const int jl = j - sg.off[s];
+    if (jl < 0 || jl >= sg.r[s]) return 0.f;
+    return load_as_float(sg.B[s], ab_dtype, (long long)(n - s * Nseg) * sg.r[s] + jl) * sg.scale[s];
+  };
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    if (i < n0) {
+      const int j = i / K, k = i - j * K;
+      A_pack[i] = from_f32<TIO>(a_val(j, k));
+    } else if (i < n1) {
+      const int t = i - n0;
+      const int j = t / N, n = t - j * N;
+      Bt_pack[t] = from_f32<TIO>(b_val(n, j));
+    } else if (i < n2) {
+      const int t = i - n1;
+      const int n = t >> 6, j = t & 63;
+      float v = b_val(n, j);
+      if (j == r_total) {
+        const int s = n / Nseg;
+        if (sg.bias[s] != nullptr) v = load_as_float(sg.bias[s], bias_dtype, n - s * Nseg);
+      }
+      Bn_pack[t] = from_f32<TIO>(v);
+    } else {
+      const int t = i - n2;
+      const int k = t >> 6, j = t & 63;
+      At_pack[t] = from_f32<TIO>(a_val(j, k));
+    }
+  }
+}
+
+cudaError_t launch_pack_seg(const void* const* A, const void* const* B, const void* const* bias,
+                            const float* scales, const int* r_each, int nseg, int ab_dtype, int bias_dtype,
+                            void* A_pack, void* Bt_pack, void* Bn_pack, void* At_pack, int K, int Nseg,
+                            int io_dtype, cudaStream_t stream) {
+  PackSegs sg = {};
+  sg.nseg = nseg;
+  int off = 0;
+  for (int s = 0; s < nseg; ++s) {
+    sg.A[s] = A[s];
+    sg.B[s] = B[s];
+    sg.bias[s] = bias ? bias[s] : nullptr;
+    sg.scale[s] = scales[s];
+    sg.r[s] = r_each[s];
+    sg.off[s] = off;
+    off += r_each[s];
+  }
+  const int total = 80 * (K + nseg * Nseg);
+  int blocks = (total + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (io_dtype == B200LORA_BF16)
+    lora_pack_seg_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
+        sg, ab_dtype, bias_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack, (__nv_bfloat16*)Bn_pack,
+        (__nv_bfloat16*)At_pack, K, Nseg, off);
+  else
+    lora_pack_seg_kernel<__half><<<blocks, 256, 0, stream>>>(
+        sg, ab_dtype, bias_dtype, (__half*)A_pack, (__half*)Bt_pack, (__half*)Bn_pack, (__half*)At_pack, K,
+        Nseg, off);
+  return cudaGetLastError();
+}
+
 }  // namespace b200

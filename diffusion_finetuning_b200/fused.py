@@ -67,6 +67,10 @@ class SiblingGroup:
                 return False
             if m.lora_down.weight.dtype != m.lora_up.weight.dtype:
                 return False
+            if m.lora_down.weight.dtype != self.layers[0].lora_down.weight.dtype:
+                return False
+            if m.linear.bias is not None and m.linear.bias.dtype != m.linear.weight.dtype:
+                return False
             r_total += m.lora_down.weight.shape[0]
         if r_total > 16:
             return False
@@ -91,7 +95,7 @@ class SiblingGroup:
         return out
 
     def pack(self, cdt, live=False):
-        """(pack buffer, A_cat, B_bd, bias_cat): b200lora_pack_lora over the concatenated factors."""
+        """(pack buffer, a bias tensor or None — only its presence matters to the GEMM call)."""
         Ls = self.layers
         key = tuple((_key(m.lora_down.weight), _key(m.lora_up.weight), float(m.scale),
                      None if m.linear.bias is None else _key(m.linear.bias)) for m in Ls) + (cdt,)
@@ -102,28 +106,25 @@ class SiblingGroup:
             return hit[1]
         N, K = Ls[0].linear.weight.shape
         dev = Ls[0].linear.weight.device
+        n = len(Ls)
         rs = [m.lora_down.weight.shape[0] for m in Ls]
-        r_total, Ncat = sum(rs), N * len(Ls)
-        with torch.no_grad():
-            A_cat = torch.cat([m.lora_down.weight.detach() for m in Ls], 0).contiguous()      # [r_total, K]
-            B_bd = torch.zeros(Ncat, r_total, dtype=A_cat.dtype, device=dev)
-            off = 0
-            for i, m in enumerate(Ls):
-                B_bd[i * N:(i + 1) * N, off:off + rs[i]] = m.lora_up.weight.detach() * float(m.scale)
-                off += rs[i]
-            bias_cat = None
-            if any(m.linear.bias is not None for m in Ls):
-                bias_cat = torch.cat([m.linear.bias.detach().to(cdt) if m.linear.bias is not None
-                                      else torch.zeros(N, dtype=cdt, device=dev) for m in Ls]).contiguous()
-            buf = torch.empty(80 * (K + Ncat), dtype=cdt, device=dev)
-            with torch.cuda.device(dev):
-                rc = nat.lib().b200lora_pack_lora(nat.ptr(A_cat), nat.ptr(B_bd), nat.dtype_code(A_cat.dtype),
-                                                  nat.ptr(bias_cat),
-                                                  nat.dtype_code(bias_cat.dtype) if bias_cat is not None else 0,
-                                                  nat.ptr(buf), K, Ncat, r_total, nat.dtype_code(cdt),
-                                                  nat.stream_ptr(dev))
-            nat.check(rc, "b200lora_pack_lora(fused)")
-        out = (buf, A_cat, B_bd, bias_cat)
+        # the pack of the concatenated problem straight from the members' factors (A rows stacked, B block-
+        # diagonal with each scale folded in, biases concatenated): ONE launch, no cat / zeros / slice launches
+        As = [m.lora_down.weight.detach().contiguous() for m in Ls]
+        Bs = [m.lora_up.weight.detach().contiguous() for m in Ls]
+        bs = [None if m.linear.bias is None else m.linear.bias.detach().contiguous() for m in Ls]
+        bias_any = next((t for t in bs if t is not None), None)
+        buf = torch.empty(80 * (K + N * n), dtype=cdt, device=dev)
+        vp = ctypes.c_void_p
+        with torch.cuda.device(dev):
+            rc = nat.lib().b200lora_pack_lora_fused(
+                (vp * n)(*[t.data_ptr() for t in As]), (vp * n)(*[t.data_ptr() for t in Bs]),
+                (vp * n)(*[None if t is None else t.data_ptr() for t in bs]),
+                (ctypes.c_float * n)(*[float(m.scale) for m in Ls]), (ctypes.c_int * n)(*rs), n,
+                nat.dtype_code(As[0].dtype), nat.dtype_code(bias_any.dtype) if bias_any is not None else 0,
+                nat.ptr(buf), K, N, nat.dtype_code(cdt), nat.stream_ptr(dev))
+        nat.check(rc, "b200lora_pack_lora(fused)")
+        out = (buf, bias_any)
         if not live:
             self._store["pack"] = (key, out)
         return out
@@ -189,15 +190,15 @@ class _FusedSiblingFn(torch.autograd.Function):
         M = x2.shape[0]
         need_grad = group.grad_on and any(ctx.needs_input_grad)
         w = group.w_cat(cdt, False)
-        pack, A_cat, B_bd, bias_cat = group.pack(cdt, live=group.grad_on and any(ctx.needs_input_grad[2:]))
+        pack, bias_flag = group.pack(cdt, live=group.grad_on and any(ctx.needs_input_grad[2:]))
         y = torch.empty((M, Ncat), dtype=cdt, device=x.device)
         T = torch.empty((M, r_total), dtype=cdt, device=x.device) if need_grad else None
         if M > 0:
             with torch.cuda.device(x.device), ops._Prof("fwd", M, K, Ncat, r_total, x2.element_size()):
                 rc = lib.b200lora_linear_fwd(
-                    nat.ptr(x2), nat.ptr(w), nat.ptr(bias_cat),
-                    nat.dtype_code(bias_cat.dtype) if bias_cat is not None else 0, nat.ptr(A_cat), nat.ptr(B_bd),
-                    nat.dtype_code(A_cat.dtype), nat.ptr(pack), 1.0, nat.ptr(y), nat.ptr(T), M, K, Ncat, r_total,
+                    nat.ptr(x2), nat.ptr(w), nat.ptr(bias_flag),          # the bias VALUES ride in the pack
+                    nat.dtype_code(bias_flag.dtype) if bias_flag is not None else 0, None, None,
+                    nat.dtype_code(ab[0].dtype), nat.ptr(pack), 1.0, nat.ptr(y), nat.ptr(T), M, K, Ncat, r_total,
                     nat.dtype_code(cdt), nat.IMPL_TC, nat.stream_ptr(x.device))
                 nat.check(rc, "b200lora_linear_fwd(fused)")
         if need_grad:

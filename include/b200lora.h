@@ -109,6 +109,19 @@ int b200lora_pack_lora(const void* A, const void* B, int ab_dtype,
                        int K, int N, int r, int io_dtype, b200lora_stream_t stream);
 
 /*
+ * The same pack for the CONCATENATED problem of up to 4 sibling layers that read one input (fused
+ * to_q/to_k/to_v), written straight from the layers' own factors: A_cat = [A_0; A_1; ...]
+ * (sum of r_each rows), B block-diagonal [nseg*Nseg, r_total] with scales[i] folded into block i, biases
+ * concatenated (bias, or any bias[i], may be NULL).  A[i] [r_each[i], K], B[i] [Nseg, r_each[i]] in ab_dtype,
+ * bias[i] [Nseg] in bias_dtype; the pointer ARRAYS are host memory (read during the call).
+ * pack: b200lora_pack_elems(K, nseg*Nseg) elements of io_dtype.
+ */
+int b200lora_pack_lora_fused(const void* const* A, const void* const* B, const void* const* bias,
+                             const float* scales, const int* r_each, int nseg, int ab_dtype,
+                             int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                             b200lora_stream_t stream);
+
+/*
  * Forward of LoraInjectedLinear — replaces lora.py:49-50
  *   `self.linear(input) + self.lora_up(self.lora_down(input)) * self.scale`
  * (3 F.linear + mul + add in the reference; one kernel here).
