@@ -4,7 +4,7 @@
 set -x
 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/plain_bench.json 2> gpurun_out/plain_bench.err && \
 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 3200 -c 6000 --csv \
-    --log-file gpurun_out/launches_bench_v9.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline \
+    --log-file gpurun_out/launches_bench_v10.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline \
     > gpurun_out/ncu_bench.json 2> gpurun_out/ncu_bench.err
 echo "launchlist rc=$?"
 cut -c1-200 gpurun_out/plain_bench.json
