@@ -496,10 +496,22 @@ def main(argv=None):
     if tr.rank == 0 and steps > marks.get("s0", steps):
         ms = t0.elapsed_time(t1) / (steps - marks["s0"])
         print(f"{ms:.2f} ms/step, {a.train_batch_size * world / ms * 1e3:.1f} samples/s on {world} GPU(s)")
+    # A captured step holds NCCL work: drop the graph and let every rank finish before anything is torn down
+    # (a communicator destroyed under a live graph can block at exit; bench.py leaves the same way).
+    tr._graphed = None
+    torch.cuda.synchronize(device)
     if world > 1:
-        dist.destroy_process_group()
+        dist.barrier()
     return 0
 
 
+def _leave(rc):
+    """Exit without interpreter teardown: communicators and graphs are process-lifetime objects here."""
+    import sys
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(int(rc or 0))
+
+
 if __name__ == "__main__":
-    raise SystemExit(main())
+    _leave(main())
