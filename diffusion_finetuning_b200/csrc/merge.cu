@@ -5,6 +5,7 @@
 // Each thread owns one 16-byte vector of a W row; the r x VEC slice of `down` it needs stays
 // in registers while it walks down a strip of rows, so per 16 B of W moved it issues one
 // 16 B load, one 16 B store and one broadcast load of up[n, 0:r].
+#include "ptx.cuh"
 #include "common.cuh"
 
 namespace b200 {
@@ -202,6 +203,9 @@ __global__ void lora_pack_kernel(const void* __restrict__ A, const void* __restr
                                  TIO* __restrict__ Bn_pack, TIO* __restrict__ At_pack, int K, int N,
                                  int r) {
   const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
+  // the GEMM that consumes this pack is the next launch on the stream: let its prologue (TMEM allocation,
+  // barrier init, descriptor prefetch) run under this grid; its griddepcontrol.wait still sees a finished pack
+  pdl_launch_dependents();
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     if (i < n0) {
       const int j = i / K, k = i - j * K;
@@ -261,6 +265,7 @@ __global__ void lora_pack_seg_kernel(const PackSegs sg, int ab_dtype, int bias_d
                                      TIO* __restrict__ At_pack, int K, int Nseg, int r_total) {
   const int N = sg.nseg * Nseg;
   const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
+  pdl_launch_dependents();      // as in lora_pack_kernel
   auto seg_of_rank = [&](int j) {
     int s = 0;
 #pragma unroll
