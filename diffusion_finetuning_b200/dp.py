@@ -256,9 +256,9 @@ class GraphedStep:
 
     `step_fn(batch_dict) -> loss tensor` must be free of host synchronisation (no .item(), optimizer
     built with capturable=True) and shape-static.  Inputs are copied into static buffers before every
-    replay; the returned loss tensor is overwritten by each replay.  Caches keyed on parameter versions
-    (the LoRA packs) are refreshed INSIDE the captured step because the warm-up steps' optimizer
-    updates invalidated them, so every replay re-packs from the live parameters.
+    replay; the returned loss tensor is overwritten by each replay.  The LoRA packs are rebuilt by every
+    training forward (ops.BaseWeightCache.lora_pack: never cached while the factors are trained), so the
+    pack launches are part of the captured step and every replay packs the live parameters.
     """
 
     def __init__(self, step_fn, example_batch: dict, warmup: int = 3, before_capture=None):
