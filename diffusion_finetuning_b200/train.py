@@ -214,9 +214,11 @@ class LoraTrainer:
             return out
 
         unet_params = lora_params(unet)
-        if not unet_params:
+        if not unet_params and placeholder_rows is None:
             raise ValueError("No lora injected.")
-        groups = [{"params": unet_params, "lr": cfg.learning_rate}]
+        # no LoRA in the UNet + placeholder rows = the inversion phase (cli_lora_pti.train_inversion, :250-405):
+        # only the rows train, through ti.PlaceholderAdamW (use clip_ti_decay=True, scheduler_first=True)
+        groups = [{"params": unet_params, "lr": cfg.learning_rate}] if unet_params else []
         models: List[nn.Module] = [unet]
         if cfg.train_text_encoder:
             if text_encoder is None:
@@ -253,10 +255,11 @@ class LoraTrainer:
             for g in groups:                    # device-resident lr: the schedule keeps working under replay
                 g["lr"] = torch.tensor(float(g["lr"]), dtype=torch.float32, device=self.device)
             opt_kw["lr"] = torch.tensor(float(cfg.learning_rate), dtype=torch.float32, device=self.device)
-        self.optimizer = torch.optim.AdamW(groups, **opt_kw)
+        self.optimizer = torch.optim.AdamW(groups, **opt_kw) if groups else None
         sched_target = self.optimizer
         if self.ti_opt is not None:             # one schedule over every group, as lr_scheduler_lora (:746-751)
-            sched_target = argparse.Namespace(param_groups=self.optimizer.param_groups + self.ti_opt.param_groups)
+            sched_target = argparse.Namespace(param_groups=(self.optimizer.param_groups if self.optimizer else [])
+                                              + self.ti_opt.param_groups)
         self.lr_scheduler = get_scheduler(cfg.lr_scheduler, sched_target, cfg.lr_warmup_steps, cfg.max_train_steps)
         self.global_step = 0          # counts loop iterations, as the reference's does (:891)
         self.last_save = 0
@@ -304,7 +307,8 @@ class LoraTrainer:
         self.arena.finish()
         if cfg.max_grad_norm is not None and cfg.max_grad_norm > 0:
             self.arena.clip_grad_norm_(cfg.max_grad_norm)
-        self.optimizer.step()
+        if self.optimizer is not None:
+            self.optimizer.step()
         if self.ti_opt is not None:
             self.ti_opt.step()
 
@@ -370,6 +374,8 @@ class LoraTrainer:
 
     # ------------------------------------------------------------------ artefacts (rank 0)
     def _save(self, unet_path, text_path=None):
+        if self.optimizer is None:              # inversion phase: nothing but the rows; the caller saves those
+            return
         L.save_lora_weight(self.unet, unet_path)
         if self.cfg.train_text_encoder and text_path:
             L.save_lora_weight(self.text_encoder, text_path, target_replace_module=["CLIPAttention"])
@@ -399,7 +405,7 @@ class LoraTrainer:
         print("\n\nLora TRAINING DONE!\n\n")
         if cfg.output_format in ("pt", "both"):
             self._save(cfg.output_dir + "/lora_weight.pt", cfg.output_dir + "/lora_weight.text_encoder.pt")
-        if cfg.output_format in ("safe", "both"):
+        if cfg.output_format in ("safe", "both") and self.optimizer is not None:
             loras = {"unet": (self.unet, {"CrossAttention", "Attention", "GEGLU"})}
             if cfg.train_text_encoder:
                 loras["text_encoder"] = (self.text_encoder, {"CLIPAttention"})
