@@ -283,6 +283,8 @@ class _LoraLinearFn(torch.autograd.Function):
             dW = (dy2.t() @ x2).to(w0.dtype)
         if need_b and has_bias:
             db = dy2.sum(0)
+        if need_x and dx is None:            # empty batch: no launch, but autograd still gets a [0, K] gradient
+            dx = torch.zeros((M, K), dtype=cdt, device=dev)
         if dx is not None and need_x:
             dx = dx.reshape(*lead, K)
             if dx.dtype != x_dtype:
