@@ -35,7 +35,7 @@ from . import lora as L
 # LR schedules — diffusers.optimization.get_scheduler (requirements.txt: diffusers>=0.9.0), used at
 # train_lora_dreambooth.py:741-747 and cli_lora_pti.py:659-664, 746-751.  All are LambdaLR factors.
 # --------------------------------------------------------------------------------------------
-def _schedule_factor(name: str, warmup: int, total: Optional[int], num_cycles: float = 0.5, power: float = 1.0):
+def _schedule_factor(name: str, warmup: int, total: Optional[int], num_cycles: float = 0.5):
     def ramp(step):
         return float(step) / float(max(1, warmup))
 

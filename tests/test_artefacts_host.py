@@ -79,3 +79,19 @@ def test_lora_add_errors_and_cpu_refusal(tmp_path):
         with pytest.raises(nat.B200LoraError):
             A.flat_axpby(torch.zeros(4))
     assert nat.lib().b200lora_flat_axpby(None, None, None, 4, 1.0, 0.0, 0, 0, None) == -6
+
+
+def test_cli_pt_to_safetensors(tmp_path):
+    from safetensors import safe_open
+    from diffusion_finetuning_b200 import cli
+    p = tmp_path / "w.pt"
+    torch.save(_pt_list(4, SHAPES), p)
+    out = tmp_path / "cli.safetensors"
+    assert cli.main(["pt_to_safetensors", str(p), "--outpath", str(out), "--set", "unet.rank=2"]) == 0
+    md = safe_open(str(out), "pt").metadata()
+    assert md["unet:0:rank"] == "2" and md["unet:1:rank"] == "2"
+    with pytest.raises(ValueError):
+        cli.main(["pt_to_safetensors", str(p), "--outpath", str(out)])
+    assert cli.main(["pt_to_safetensors", str(p), "--outpath", str(out), "--overwrite"]) == 0
+    with pytest.raises(SystemExit):
+        cli.main(["pt_to_safetensors", str(p), "--outpath", str(out), "--overwrite", "--set", "rank8"])
