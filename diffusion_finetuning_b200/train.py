@@ -120,11 +120,16 @@ class DDPMNoiseSchedule:
         else:
             raise NotImplementedError(f"{beta_schedule} does is not implemented for DDPMNoiseSchedule")
         self.alphas_cumprod = torch.cumprod(1.0 - betas, dim=0)
+        self._on_device = {}
         self.num_train_timesteps = num_train_timesteps
         self.prediction_type = prediction_type
 
     def _coefs(self, like, timesteps):
-        ac = self.alphas_cumprod.to(device=like.device, dtype=like.dtype)[timesteps]
+        key = (like.device, like.dtype)
+        table = self._on_device.get(key)
+        if table is None:       # one host->device copy per (device, dtype), not one per step
+            table = self._on_device[key] = self.alphas_cumprod.to(device=like.device, dtype=like.dtype)
+        ac = table[timesteps]
         shape = (-1,) + (1,) * (like.dim() - 1)
         return (ac ** 0.5).reshape(shape), ((1 - ac) ** 0.5).reshape(shape)
 
