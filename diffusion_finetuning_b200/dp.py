@@ -312,7 +312,9 @@ class ArenaAdamW:
                 raise nat.B200LoraError(f"ArenaAdamW needs fp32 LoRA parameters (got {p.dtype}); keep fp32 masters "
                                         "and run the model under autocast")
         self.arena = arena
-        self.lr, self.betas, self.eps, self.weight_decay = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        self.betas, self.eps, self.weight_decay = (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        # torch layout (one group) so LR schedulers that walk `param_groups` drive this optimizer too
+        self.param_groups = [{"params": arena.params, "lr": float(lr), "initial_lr": float(lr)}]
         self.max_grad_norm = None if max_grad_norm is None else float(max_grad_norm)
         n = arena.flat.numel()
         self.flat_p = torch.empty(n, dtype=torch.float32, device=arena.device)
@@ -324,6 +326,14 @@ class ArenaAdamW:
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=arena.device)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=arena.device)
         self.scratch = torch.zeros(2, dtype=torch.float32, device=arena.device)   # [sum g^2, step count]
+
+    @property
+    def lr(self) -> float:
+        return float(self.param_groups[0]["lr"])
+
+    @lr.setter
+    def lr(self, value):
+        self.param_groups[0]["lr"] = float(value)
 
     def _check_homes(self):
         # monkeypatch_* / weight loading re-assign `.weight` with fresh Parameters: the arena (and this

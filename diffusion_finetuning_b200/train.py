@@ -190,6 +190,7 @@ class TrainConfig:
     seed: Optional[int] = None
     learning_rate_ti: Optional[float] = None     # continue_inversion_lr / ti_lr (cli_lora_pti.py:715-722)
     clip_ti_decay: bool = False                  # perform_tuning has no norm decay; train_inversion has (:317)
+    arena_optimizer: bool = False                # clip + AdamW over the flat arenas in one C-ABI call (dp.ArenaAdamW)
 
 
 class LoraTrainer:
@@ -256,11 +257,26 @@ class LoraTrainer:
                       eps=cfg.adam_epsilon)
         if on_cuda:
             opt_kw.update(fused=True, capturable=self.graph_ok)
-        if self.graph_ok:
+        group_lrs = [float(g["lr"]) for g in groups]
+        if self.graph_ok and not cfg.arena_optimizer:
             for g in groups:                    # device-resident lr: the schedule keeps working under replay
                 g["lr"] = torch.tensor(float(g["lr"]), dtype=torch.float32, device=self.device)
             opt_kw["lr"] = torch.tensor(float(cfg.learning_rate), dtype=torch.float32, device=self.device)
-        self.optimizer = torch.optim.AdamW(groups, **opt_kw) if groups else None
+        if cfg.arena_optimizer:
+            # one kernel pair over the flat parameter/gradient arenas instead of clip_grad_norm_ + multi-tensor AdamW
+            if len(groups) != 1 or self.ti_opt is not None or not on_cuda or any(
+                    lr != float(cfg.learning_rate) for lr in group_lrs):
+                raise ValueError("arena_optimizer needs ONE learning rate over all trainable parameters on a CUDA "
+                                 "device (no separate text-encoder lr, no placeholder rows)")
+            if self.graph_ok and cfg.lr_scheduler != "constant":
+                raise ValueError("arena_optimizer takes lr as a launch argument: with use_cuda_graph the schedule must be "
+                                 "'constant' (a captured launch replays the lr it was captured with)")
+            self.optimizer = dp.ArenaAdamW(self.arena, lr=cfg.learning_rate, betas=(cfg.adam_beta1, cfg.adam_beta2),
+                                           eps=cfg.adam_epsilon, weight_decay=cfg.adam_weight_decay,
+                                           max_grad_norm=cfg.max_grad_norm if cfg.max_grad_norm and cfg.max_grad_norm > 0
+                                           else None)
+        else:
+            self.optimizer = torch.optim.AdamW(groups, **opt_kw) if groups else None
         sched_target = self.optimizer
         if self.ti_opt is not None:             # one schedule over every group, as lr_scheduler_lora (:746-751)
             sched_target = argparse.Namespace(param_groups=(self.optimizer.param_groups if self.optimizer else [])
@@ -310,8 +326,8 @@ class LoraTrainer:
     def _update(self):
         cfg = self.cfg
         self.arena.finish()
-        if cfg.max_grad_norm is not None and cfg.max_grad_norm > 0:
-            self.arena.clip_grad_norm_(cfg.max_grad_norm)
+        if cfg.max_grad_norm is not None and cfg.max_grad_norm > 0 and not cfg.arena_optimizer:
+            self.arena.clip_grad_norm_(cfg.max_grad_norm)      # (ArenaAdamW clips inside its own launch)
         if self.optimizer is not None:
             self.optimizer.step()
         if self.ti_opt is not None:
@@ -329,6 +345,14 @@ class LoraTrainer:
         optimizer state, library workspaces); a training job must not see those updates, so parameters and
         optimizer state are put back IN PLACE afterwards (the graph holds their addresses)."""
         params = self.arena.params
+        if isinstance(self.optimizer, dp.ArenaAdamW):
+            o = self.optimizer
+            keep = [t.clone() for t in (o.flat_p, o.exp_avg, o.exp_avg_sq, o.scratch)]
+            graphed = dp.GraphedStep(self._whole_step, b)
+            with torch.no_grad():
+                for t, k in zip((o.flat_p, o.exp_avg, o.exp_avg_sq, o.scratch), keep):
+                    t.copy_(k)
+            return graphed
         saved_p = [p.detach().clone() for p in params]
         saved_s = {id(p): {k: v.clone() for k, v in self.optimizer.state[p].items() if torch.is_tensor(v)}
                    for p in params if p in self.optimizer.state}

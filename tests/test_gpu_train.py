@@ -52,12 +52,15 @@ def _state(unet):
             for p in (m.lora_up.weight, m.lora_down.weight)]
 
 
-@pytest.mark.parametrize("graph", [False, True])
-def test_trainer_equals_plain_torch_loop(graph, tmp_path):
+@pytest.mark.parametrize("graph,arena_opt", [(False, False), (True, False), (False, True)])
+def test_trainer_equals_plain_torch_loop(graph, arena_opt, tmp_path):
+    """arena_opt: clip + AdamW over the flat arenas in one C-ABI call (dp.ArenaAdamW) instead of
+    arena.clip_grad_norm_ + torch's fused AdamW; the LR schedule drives it through `param_groups`."""
+    from diffusion_finetuning_b200 import dp
     data = _batches(6)
     unet, _ = _unet()
-    tr = T.LoraTrainer(unet, _cfg(tmp_path, use_cuda_graph=graph))
-    assert tr.graph_ok == graph
+    tr = T.LoraTrainer(unet, _cfg(tmp_path, use_cuda_graph=graph, arena_optimizer=arena_opt))
+    assert tr.graph_ok == graph and isinstance(tr.optimizer, dp.ArenaAdamW) == arena_opt
     losses = [tr.train_step(b).item() for b in data]
     # the reference's loop with stock pieces: autograd .grad, clip_grad_norm_, AdamW, LambdaLR
     ref_unet, params = _unet()
@@ -244,3 +247,19 @@ def test_inversion_phase_through_the_trainer(tmp_path):
     assert torch.equal(emb.weight[no_upd], table0[no_upd])
     tr.save_final()                                               # nothing LoRA to write in this phase
     assert not any(n.startswith("lora_weight") for n in os.listdir(tmp_path))
+
+
+def test_arena_optimizer_under_graph_needs_constant_lr_and_matches_eager(tmp_path):
+    data = _batches(5)
+    with pytest.raises(ValueError):
+        T.LoraTrainer(_unet()[0], _cfg(tmp_path, use_cuda_graph=True, arena_optimizer=True, lr_scheduler="linear"))
+    runs = []
+    for graph in (False, True):
+        unet, _ = _unet()
+        tr = T.LoraTrainer(unet, _cfg(tmp_path, use_cuda_graph=graph, arena_optimizer=True, lr_scheduler="constant",
+                                      lr_warmup_steps=0))
+        losses = [tr.train_step(b).item() for b in data]
+        runs.append((losses, _state(unet)))
+    assert runs[0][0] == pytest.approx(runs[1][0], rel=2e-4)
+    for a, b in zip(runs[0][1], runs[1][1]):
+        assert rel_err(a, b) < 1e-2
