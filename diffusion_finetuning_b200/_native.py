@@ -28,6 +28,9 @@ SIGNATURES = {
     "b200lora_version": (_i32, []),
     "b200lora_last_error": (ctypes.c_char_p, []),
     "b200lora_tc_supported": (_i32, []),
+    "b200lora_watchdog_code": (ctypes.c_uint, []),
+    "b200lora_peek_cuda_error": (_i32, []),
+    "b200lora_debug_timeline": (None, [_vp, _i32]),
     "b200lora_lora_gemm": (_i32, [_vp, _i64, _vp, _i64, _i32, _vp, _i32, _vp, _i64, _i64, _vp, _vp,
                                   _i64, _i64, _i32, _vp, _f32, _vp, _i64, _vp, _i64, _i32, _i32,
                                   _i32, _i32, _i32, _vp]),
@@ -45,7 +48,7 @@ SIGNATURES = {
     "b200lora_flat_axpby": (_i32, [_vp, _vp, _vp, _i64, _f32, _f32, _i32, _i32, _vp]),
     "b200lora_ti_grad_rows": (_i32, [_vp, _vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp]),
     "b200lora_ti_step": (_i32, [_vp, _i32, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i32, _f32, _f32, _f32, _f32, _f32,
-                                _f32, _f32, _vp, _vp]),
+                                _f32, _f32, _vp, _vp, _vp, _vp]),
     "b200lora_linear_bwd_dx_fused": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_lora_grads_fused": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp,
                                          _i32, _vp]),
@@ -56,9 +59,18 @@ SIGNATURES = {
     "b200lora_conv2d_zcat": (_i32, [_vp, _vp, _i32, _f32, _vp, _vp, _i64, _i32, _i32, _i32, _vp]),
     "b200lora_conv2d_grad_a": (_i32, [_vp, _vp, _f32, _vp] + [_i32] * 14 + [_vp]),
     "b200lora_merge": (_i32, [_vp, _vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_merge_batch_workspace": (_i64, [_i32]),
+    "b200lora_merge_batch_plan": (_i32, [_vp, _i32, _i32, _vp, _i64, _vp, _vp]),
+    "b200lora_merge_batch_run": (_i32, [_vp, _i32, _i64, _i32, _f32, _i32, _i32, _vp]),
     "b200lora_absmean_accum": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_svd_epilogue": (_i32, [_vp, _vp, _vp, _f32, _i32, _i32, _i32, _i32, _vp]),
 }
+
+
+class MergeItem(ctypes.Structure):
+    """b200lora_merge_item of include/b200lora.h."""
+    _fields_ = [("Win", _vp), ("Wout", _vp), ("up", _vp), ("down", _vp),
+                ("N", ctypes.c_int32), ("K", ctypes.c_int32), ("r", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class B200LoraError(RuntimeError):

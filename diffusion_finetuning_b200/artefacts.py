@@ -3,6 +3,7 @@ the arithmetic runs on the GPU.
 
   * `lora_add(...)`                 cli_lora_add.py:17-114  (`lpl` list mix; `upl` merge into a pipeline)
   * `convert(...)`                  cli_pt_to_safetensors.py:19-77  (.pt lists / TI dicts -> one .safetensors)
+  * `svd_distill(...)`              cli_svd.py:29-111  (`lora_distill`: rank-r factors of tuned − base, whole model)
   * `save_lora_weight_streamed`     lora.py:201-213  — one cast launch + ONE device→host copy for all 2·L
                                     tensors instead of 2·L casts and 2·L copies
   * `save_safeloras_streamed`       lora.py:228-258  — same for the safetensors writer
@@ -129,6 +130,70 @@ def lora_add(path_1: str, path_2: str, output_path: str, alpha: float = 0.5, mod
         return pipe
     print("Unknown mode", mode)
     raise ValueError(f"Unknown mode {mode}")
+
+
+# --------------------------------------------------------------------------------------------
+# cli_svd (`lora_distill`)
+# --------------------------------------------------------------------------------------------
+SVD_UNET_TARGETS = ["CrossAttention", "Attention", "GEGLU"]       # cli_svd.py:46-48
+SVD_TEXT_TARGETS = ["CLIPAttention"]                              # cli_svd.py:49
+
+
+def extract_linear_weights(model, target_replace_module):
+    """The `.weight` of every nn.Linear under the target classes, in discovery order (cli_svd.py:19-26)."""
+    return [child.weight for _, _, child in L._find_modules(model, target_replace_module, search_class=[nn.Linear])]
+
+
+def _default_fp16_pipeline_loader(path, device):
+    try:
+        from diffusers import StableDiffusionPipeline
+    except ImportError as exc:                  # the reference imports diffusers at module top (cli_svd.py:2)
+        raise ImportError("svd_distill loads two diffusers pipelines; diffusers is not installed — pass "
+                          "`load_pipeline=` returning an object with .unet / .text_encoder") from exc
+    return StableDiffusionPipeline.from_pretrained(path, torch_dtype=torch.float16).to(device)
+
+
+def svd_distill_weights(tuned: Sequence[torch.Tensor], base: Sequence[torch.Tensor], rank: int = 4,
+                        clamp_quantile: float = 0.99, device=None) -> List[torch.Tensor]:
+    """`[U0, Vh0, U1, Vh1, ...]` (fp32, on `device`) for `zip(base, tuned)` — the loop of cli_svd.py:56-84 /
+    :86-108.  The difference is taken in the WEIGHTS' dtype (`tuned - ori`, :59-63: fp16 pipelines, so ΔW is
+    rounded to fp16 before it is widened), each ΔW goes through `ops.svd_distill_matrix` (cuSOLVER gesvd, economy
+    size — the reference's full `U [N, N]` is never used — + the scale/clamp epilogue kernel)."""
+    from . import ops
+    dev = torch.device(device) if device is not None else _cuda_device(*tuned)
+    out = []
+    with torch.no_grad():
+        for ori, new in zip(base, tuned):
+            diff = new.detach().to(dev) - ori.detach().to(dev)        # same rounding on either device (one IEEE op)
+            U, Vh = ops.svd_distill_matrix(diff, rank=rank, clamp_quantile=clamp_quantile)
+            out += [U, Vh]
+    return out
+
+
+def svd_distill(target_model: str, base_model: str, rank: int = 4, clamp_quantile: float = 0.99,
+                device: str = "cuda:0", save_path: str = "svd_distill.pt",
+                load_pipeline: Optional[Callable] = None):
+    """cli_svd.svd_distill (cli_svd.py:29-111): rank-`rank` LoRA factors of (tuned − base) for every Linear under
+    {"CrossAttention", "Attention", "GEGLU"} of the UNet and {"CLIPAttention"} of the text encoder; saves the UNet
+    list to `save_path` and the text-encoder list to `<save_path minus .pt>.text_encoder.pt` (:110-111).
+    `load_pipeline(path, device)` replaces `StableDiffusionPipeline.from_pretrained(path, torch_dtype=float16)`."""
+    load = load_pipeline or _default_fp16_pipeline_loader
+    pipe_base = load(base_model, device)
+    pipe_tuned = load(target_model, device)
+    ori_unet = extract_linear_weights(pipe_base.unet, SVD_UNET_TARGETS)
+    ori_clip = extract_linear_weights(pipe_base.text_encoder, SVD_TEXT_TARGETS)
+    tuned_unet = extract_linear_weights(pipe_tuned.unet, SVD_UNET_TARGETS)
+    tuned_clip = extract_linear_weights(pipe_tuned.text_encoder, SVD_TEXT_TARGETS)
+    dev = torch.device(device) if torch.device(device).type == "cuda" else _cuda_device(*tuned_unet)
+    uds_unet = svd_distill_weights(tuned_unet, ori_unet, rank, clamp_quantile, dev)
+    uds_clip = svd_distill_weights(tuned_clip, ori_clip, rank, clamp_quantile, dev)
+    home = torch.device(device)
+    if home != dev:                              # the reference leaves the factors on `device`
+        uds_unet = [t.to(home) for t in uds_unet]
+        uds_clip = [t.to(home) for t in uds_clip]
+    torch.save(uds_unet, save_path)
+    torch.save(uds_clip, L._text_lora_path(save_path))
+    return uds_unet, uds_clip
 
 
 # --------------------------------------------------------------------------------------------

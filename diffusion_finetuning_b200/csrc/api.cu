@@ -68,13 +68,17 @@ cudaError_t launch_merge(const void*, void*, const void*, const void*, float, in
                          float*, cudaStream_t);
 cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, int, int,
                                 cudaStream_t);
+struct MergeItem { const void* Win; void* Wout; const void* up; const void* down; int N, K, r, tile0, tiles_k, pad; };
+long long merge_batch_plan(MergeItem*, int, int);
+cudaError_t launch_merge_batch(const MergeItem*, int, int, int, float, int, int, int, cudaStream_t);
 cudaError_t launch_arena_adamw(float*, float*, float*, float*, long long, float, float, float, float, float,
                                float, float*, cudaStream_t);
 cudaError_t launch_flat_axpby(const void*, const void*, void*, long long, float, float, int, int, cudaStream_t);
 cudaError_t launch_ti_grad_rows(const void*, const long long*, long long, int, const long long*, int, float*, int,
                                 cudaStream_t);
 cudaError_t launch_ti_step(void*, int, int, const long long*, int, float*, const float*, float*, float*, float,
-                           float, float, float, float, float, float, float, float*, cudaStream_t);
+                           float, float, float, float, float, float, float, float*, const float*, float*,
+                           cudaStream_t);
 
 // ---------------------------------------------------------------------------------------
 // device info
@@ -849,14 +853,16 @@ extern "C" int b200lora_ti_grad_rows(const void* dY, const int64_t* token_ids, i
 extern "C" int b200lora_ti_step(void* table, int table_dtype, int D, const int64_t* rows, int P, float* master_rows,
                                 const float* grad_rows, float* exp_avg, float* exp_avg_sq, int step, float lr,
                                 float beta1, float beta2, float eps, float weight_decay, float lambda_,
-                                float target_norm, float* norms_out, b200lora_stream_t stream_) {
+                                float target_norm, float* norms_out, const float* lr_dev, float* step_dev,
+                                b200lora_stream_t stream_) {
   g_err[0] = 0;
   if (!table || !rows || !master_rows || !grad_rows || !exp_avg || !exp_avg_sq) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (!valid_dtype(table_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
-  if (D < 1 || P < 1 || step < 1) { set_error("ti_step: bad shape or step (D=%d, P=%d, step=%d)", D, P, step); return B200LORA_E_SHAPE; }
+  if (D < 1 || P < 1 || (!step_dev && step < 1)) { set_error("ti_step: bad shape or step (D=%d, P=%d, step=%d)", D, P, step); return B200LORA_E_SHAPE; }
   cudaError_t e = launch_ti_step(table, table_dtype, D, reinterpret_cast<const long long*>(rows), P, master_rows,
                                  grad_rows, exp_avg, exp_avg_sq, (float)step, lr, beta1, beta2, eps, weight_decay,
-                                 lambda_, target_norm, norms_out, reinterpret_cast<cudaStream_t>(stream_));
+                                 lambda_, target_norm, norms_out, lr_dev, step_dev,
+                                 reinterpret_cast<cudaStream_t>(stream_));
   if (e != cudaSuccess) { set_error("ti_step launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
@@ -882,6 +888,54 @@ extern "C" int b200lora_merge(const void* Win, void* Wout, const void* up, const
 #undef M1
 #undef M2
   if (e != cudaSuccess) { set_error("merge launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
+}
+
+extern "C" int64_t b200lora_merge_batch_workspace(int n_items) {
+  return n_items > 0 ? (int64_t)n_items * (int64_t)sizeof(MergeItem) : 0;
+}
+
+// host-side half: validate the items and write the device-format problem table into `table_host`
+extern "C" int b200lora_merge_batch_plan(const b200lora_merge_item* items, int n_items, int w_dtype,
+                                         void* table_host, int64_t table_bytes, int64_t* total_tiles,
+                                         int* max_rank) {
+  g_err[0] = 0;
+  if (!items || n_items < 1 || !table_host || !total_tiles || !max_rank) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(w_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (table_bytes < b200lora_merge_batch_workspace(n_items)) { set_error("merge_batch_plan: table buffer too small"); return B200LORA_E_ARG; }
+  const int vec = 16 / dtype_size(w_dtype);
+  MergeItem* host = static_cast<MergeItem*>(table_host);
+  int max_r = 0;
+  for (int i = 0; i < n_items; ++i) {
+    const b200lora_merge_item& s = items[i];
+    if (!s.Win || !s.Wout || !s.up || !s.down) { set_error("merge_batch: item %d has a null pointer", i); return B200LORA_E_ARG; }
+    if (s.N < 1 || s.K < 1 || s.r < 1) { set_error("merge_batch: item %d has a bad shape", i); return B200LORA_E_SHAPE; }
+    if (s.K % vec || !aligned16(s.Win) || !aligned16(s.Wout)) {
+      set_error("merge_batch: item %d needs K %% %d == 0 and 16-byte aligned W", i, vec); return B200LORA_E_ALIGN;
+    }
+    host[i] = MergeItem{s.Win, s.Wout, s.up, s.down, s.N, s.K, s.r, 0, 0, 0};
+    if (s.r > max_r) max_r = s.r;
+  }
+  const long long tiles = merge_batch_plan(host, n_items, w_dtype);
+  if (tiles > 0x7fffffffll) { set_error("merge_batch: too many tiles"); return B200LORA_E_SHAPE; }
+  *total_tiles = tiles;
+  *max_rank = max_r;
+  return 0;
+}
+
+// device-side half: ONE launch over the table (already resident in device memory)
+extern "C" int b200lora_merge_batch_run(const void* table_dev, int n_items, int64_t total_tiles, int max_rank,
+                                        float alpha, int w_dtype, int lora_dtype, b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (n_items == 0 || total_tiles == 0) return 0;
+  if (!table_dev || n_items < 0 || total_tiles < 0 || total_tiles > 0x7fffffffll || max_rank < 1) { set_error("merge_batch_run: bad argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(w_dtype) || !valid_dtype(lora_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (!aligned16(table_dev)) { set_error("merge_batch_run: table must be 16-byte aligned"); return B200LORA_E_ALIGN; }
+  DevInfo di = dev_info();
+  cudaError_t e = launch_merge_batch(static_cast<const MergeItem*>(table_dev), n_items, (int)total_tiles, max_rank,
+                                     alpha, w_dtype, lora_dtype, di.sms > 0 ? di.sms : 148,
+                                     reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("merge_batch launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
 

@@ -69,10 +69,23 @@ __global__ void __launch_bounds__(256) ti_step_kernel(TW* __restrict__ table, in
                                                       float* __restrict__ m, float* __restrict__ v,
                                                       float step, float lr, float b1, float b2, float eps,
                                                       float wd, float lambda_, float target_norm,
-                                                      float* __restrict__ norms_out, int P) {
+                                                      float* __restrict__ norms_out, int P,
+                                                      const float* __restrict__ lr_dev,
+                                                      float* __restrict__ step_dev) {
   __shared__ float ws[8];
   const int p = blockIdx.x;
   const long long row = rows[p];
+  // Replayable form (the step lives in a captured CUDA graph): the learning rate and the per-row step count
+  // are read from device memory, so an LR schedule and the bias correction keep moving under replay.
+  if (lr_dev != nullptr) {
+    lr = lr_dev[0];
+    if (lambda_ >= 0.f) lambda_ = fminf(1.f, 100.f * lr);      // cli_lora_pti.py:318
+  }
+  if (step_dev != nullptr) {
+    step = step_dev[p] + 1.f;
+    __syncthreads();
+    if (threadIdx.x == 0) step_dev[p] = step;
+  }
   const float bc1 = 1.f - powf(b1, step);
   const float bc2_sqrt = sqrtf(1.f - powf(b2, step));
   const float step_size = lr / bc1;
@@ -125,9 +138,10 @@ cudaError_t launch_ti_grad_rows(const void* dY, const long long* ids, long long 
 cudaError_t launch_ti_step(void* table, int w_dtype, int D, const long long* rows, int P, float* master,
                            const float* g, float* m, float* v, float step, float lr, float b1, float b2,
                            float eps, float wd, float lambda_, float target_norm, float* norms_out,
-                           cudaStream_t stream) {
+                           const float* lr_dev, float* step_dev, cudaStream_t stream) {
 #define RUN(TW) ti_step_kernel<TW><<<P, 256, 0, stream>>>(static_cast<TW*>(table), D, rows, master, g, m, v, step, \
-                                                          lr, b1, b2, eps, wd, lambda_, target_norm, norms_out, P)
+                                                          lr, b1, b2, eps, wd, lambda_, target_norm, norms_out, P, \
+                                                          lr_dev, step_dev)
   if (w_dtype == B200LORA_F32) RUN(float);
   else if (w_dtype == B200LORA_F16) RUN(__half);
   else RUN(__nv_bfloat16);

@@ -113,28 +113,28 @@ class LoraGradArena:
                 oA, nA, bA = self._slot[id(layer.lora_down.weight)]
                 layer._grad_sink = ops.GradSink(
                     self.flat[oA:oA + nA].view_as(layer.lora_down.weight),
-                    self.flat[oB:oB + nB].view_as(layer.lora_up.weight),
-                    self._make_sink_ready(bA, bB))
+                    self.flat[oB:oB + nB].view_as(layer.lora_up.weight))
         self._layers = layers
+        # bench.py: a callable returning a fresh recordable CUDA event; finish() then stamps one event before the
+        # join of the exchange stream and one after it (exposed = non-overlapped all-reduce time per step)
+        self.exposure_probe = None
+        self.exposure_events = []
         self.zero()
 
     # ------------------------------------------------------------------ bookkeeping
     def _make_hook(self, bi):
         def hook(param):
-            # autograd accumulated into p.grad (a view of the arena for fp32 parameters; for
-            # low-precision parameters the value is folded into the fp32 arena here)
+            # Runs once per backward per parameter, after every use of the layer has been differentiated —
+            # also when the Function returned no gradient because its kernel added straight into the arena
+            # (ops.GradSink); it is the ONLY "slice final" signal.  Otherwise autograd accumulated into p.grad
+            # (a view of the arena for fp32 parameters; for low-precision parameters the value is folded into
+            # the fp32 arena here)
             if param.dtype != torch.float32:
                 o, n, _ = self._slot[id(param)]
                 self.flat[o:o + n].add_(param.grad.reshape(-1).float())
                 param.grad.zero_()      # folded; finish() writes the reduced value back
             self._ready(bi)
         return hook
-
-    def _make_sink_ready(self, bA, bB):
-        def ready():
-            self._ready(bA)
-            self._ready(bB)
-        return ready
 
     def _ready(self, bi):
         b = self.buckets[bi]
@@ -193,6 +193,10 @@ class LoraGradArena:
         for b in self.buckets:
             if not b.fired:
                 self._fire(b)
+        probe = self.exposure_probe if (self._comm is not None and self._comm_used) else None
+        if probe is not None:
+            e0 = probe()
+            e0.record(torch.cuda.current_stream(self.device))
         for b in self.buckets:
             if b.work is not None:
                 b.work.wait()
@@ -202,6 +206,10 @@ class LoraGradArena:
             # joined the capture must not be waited on)
             torch.cuda.current_stream(self.device).wait_stream(self._comm)
             self._comm_used = False
+        if probe is not None:
+            e1 = probe()
+            e1.record(torch.cuda.current_stream(self.device))
+            self.exposure_events.append((e0, e1))
         if self.world > 1 and self.average and self._comm is None:
             self.flat.mul_(1.0 / self.world)        # gloo has no AVG
         for dt, lp in self._lowp.items():

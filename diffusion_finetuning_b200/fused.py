@@ -250,10 +250,7 @@ class _FusedSiblingFn(torch.autograd.Function):
                         rc = lib.b200lora_lora_grads_fused(dyp, ldp, n, nat.ptr(x2), nat.ptr(T), nat.ptr(dT), sc,
                                                            dap, dbp, M, K, N, re, io, stream)
                         nat.check(rc, "b200lora_lora_grads_fused")
-                    if use_sink:
-                        for s in sinks:
-                            s.ready()
-                    else:
+                    if not use_sink:
                         for i in range(n):
                             if ctx.needs_input_grad[2 + 2 * i]:
                                 grads[2 * i] = dA32[i].to(ab_dtypes[i])

@@ -262,6 +262,10 @@ def _inject(model, targets, search, r, loras, dropout_p, scale):
         layer.lora_up.weight.requires_grad = True
         layer.lora_down.weight.requires_grad = True
         names.append(name)
+    # remembered for the savers (train.LoraTrainer): extract_lora_ups_down only walks descendants of the classes it
+    # is given, so a checkpoint of an extended / custom injection must be written with the set it was injected under
+    prior = getattr(model, "_lora_injected_targets", None)
+    model._lora_injected_targets = set(targets) | (set(prior) if prior else set())
     return params, names
 
 
@@ -431,23 +435,34 @@ def load_safeloras_both(path, device="cpu"):
 def weight_apply_lora(model, loras, target_replace_module=DEFAULT_TARGET_REPLACE, alpha=1.0):
     """W <- W + alpha * (up @ down).type(W.dtype) for every targeted nn.Linear
     (reference lora.py:410-424), on the bandwidth-bound merge kernel.  `loras` is consumed."""
-    for _, _, child in _find_modules(model, target_replace_module, search_class=[nn.Linear]):
-        weight = child.weight
-        up = loras.pop(0).detach().to(weight.device)
-        down = loras.pop(0).detach().to(weight.device)
-        child.weight = nn.Parameter(ops.merge_lora_weight(weight, up, down, alpha))
+    children = [child for _, _, child in _find_modules(model, target_replace_module, search_class=[nn.Linear])]
+    ups, downs = [], []
+    for child in children:                       # the reference pops up, then down, per layer (lora.py:419-420)
+        ups.append(loras.pop(0).detach().to(child.weight.device))
+        downs.append(loras.pop(0).detach().to(child.weight.device))
+    # every matrix of the model in one launch (b200lora_merge_batch) instead of one launch per layer
+    merged = ops.merge_lora_weights([c.weight for c in children], ups, downs, alpha)
+    for child, w in zip(children, merged):
+        child.weight = nn.Parameter(w)           # fresh Parameter, requires_grad=True, as lora.py:423
 
 
 def collapse_lora(model, alpha=1.0):
     """Fold every injected LoRA into its base weight in place (upstream helper)."""
+    by_alpha = {}
     for m in model.modules():
         if isinstance(m, LoraInjectedLinear):
+            by_alpha.setdefault(float(alpha * m.scale), []).append(m)
+    for a, mods in by_alpha.items():             # one launch per distinct alpha·scale (normally one)
+        ups, downs = [], []
+        for m in mods:
             up, down = m.lora_up.weight.data, m.lora_down.weight.data
             if not isinstance(m.selector, nn.Identity):
                 down = m.selector.weight.data.to(down.dtype) @ down
-            m.linear.weight = nn.Parameter(
-                ops.merge_lora_weight(m.linear.weight, up, down, alpha * m.scale),
-                requires_grad=m.linear.weight.requires_grad)
+            ups.append(up)
+            downs.append(down)
+        merged = ops.merge_lora_weights([m.linear.weight for m in mods], ups, downs, a)
+        for m, w in zip(mods, merged):
+            m.linear.weight = nn.Parameter(w, requires_grad=m.linear.weight.requires_grad)
 
 
 # ---------------------------------------------------------------------------------------------

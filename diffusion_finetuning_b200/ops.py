@@ -148,12 +148,17 @@ class _Prof:
 class GradSink:
     """Where the gradient reductions of one injected layer land: fp32 slices of a flat gradient
     arena (dp.LoraGradArena).  With a sink the dA/dB kernel ADDS straight into the arena (no
-    zero-fill, cast or autograd accumulate launches) and `ready()` tells the arena that this
-    layer's slice is final for the step, which is what fires a bucket's all-reduce."""
-    __slots__ = ("dA", "dB", "ready")
+    zero-fill, cast or autograd accumulate launches) and the autograd Function returns no gradient
+    for the factors.  "This slice is final for the step" — what fires a bucket's all-reduce — is
+    NOT signalled from here: autograd runs the parameter's AccumulateGrad node (and with it the
+    arena's post-accumulate hook) exactly once per backward, after EVERY use of the layer has run
+    its backward, also when the gradient it receives is undefined.  A layer that runs twice in one
+    step (a text encoder called twice, shared modules) is therefore exchanged after its last
+    contribution, never between two of them."""
+    __slots__ = ("dA", "dB")
 
-    def __init__(self, dA, dB, ready):
-        self.dA, self.dB, self.ready = dA, dB, ready
+    def __init__(self, dA, dB):
+        self.dA, self.dB = dA, dB
 
 
 class _LoraLinearFn(torch.autograd.Function):
@@ -271,9 +276,7 @@ class _LoraLinearFn(torch.autograd.Function):
                                                      io_code, 1 if deterministic else 0, nat.ptr(ws),
                                                      ws_bytes, stream)
                         nat.check(rc, "b200lora_lora_grads")
-                if use_sink:
-                    sink.ready()                       # grads live in the arena, not in autograd
-                else:
+                if not use_sink:                       # (with a sink the grads live in the arena, not in autograd)
                     dA = dA32.to(A.dtype) if need_A else None
                     dB = dB32.to(B.dtype) if need_B else None
         dW = db = None
@@ -343,6 +346,97 @@ def merge_lora_weight(weight, up, down, alpha=1.0):
                                     nat.stream_ptr(dev))
         nat.check(rc, "b200lora_merge")
         return out if home == dev else out.to(home)
+
+
+class MergePlan:
+    """The problem table of a whole-model merge, resident on the device (b200lora_merge_batch_plan / _run):
+    every (Win, Wout, up, down) of one (device, weight dtype, LoRA dtype) group.  `run(alpha)` is ONE launch;
+    the plan can be re-run (a sweep over alpha: Win = pristine base, Wout = live weight)."""
+
+    def __init__(self, wins, wouts, ups, downs):
+        import ctypes
+        lib = nat.lib()
+        n = len(wins)
+        if n == 0:
+            raise RuntimeError("merge: empty plan")
+        self.dev = wins[0].device
+        self.wdt, self.ldt = wins[0].dtype, ups[0].dtype
+        self.keep = (list(wins), list(wouts), list(ups), list(downs))      # the table holds raw pointers
+        items = (nat.MergeItem * n)()
+        for i, (wi, wo, u, d) in enumerate(zip(wins, wouts, ups, downs)):
+            N, K = wi.shape
+            r = u.shape[1]
+            if u.shape != (N, r) or d.shape != (r, K) or wo.shape != wi.shape:
+                raise RuntimeError(f"merge: shapes up {tuple(u.shape)} / down {tuple(d.shape)} do not "
+                                   f"match weight {(N, K)}")
+            for t in (wi, wo, u, d):
+                if t.device != self.dev or not t.is_contiguous():
+                    raise RuntimeError("merge: every tensor of a plan must be contiguous and on the plan's device")
+            if wi.dtype != self.wdt or wo.dtype != self.wdt or u.dtype != self.ldt or d.dtype != self.ldt:
+                raise RuntimeError("merge: a plan holds ONE weight dtype and ONE LoRA dtype")
+            items[i] = nat.MergeItem(wi.data_ptr(), wo.data_ptr(), u.data_ptr(), d.data_ptr(), N, K, r, 0)
+        nbytes = int(lib.b200lora_merge_batch_workspace(n))
+        host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        tiles, max_r = ctypes.c_int64(0), ctypes.c_int(0)
+        rc = lib.b200lora_merge_batch_plan(items, n, nat.dtype_code(self.wdt), ctypes.c_void_p(host.data_ptr()), nbytes,
+                                           ctypes.byref(tiles), ctypes.byref(max_r))
+        if rc != 0:
+            nat.check(rc, "b200lora_merge_batch_plan")
+        self.n, self.tiles, self.max_r = n, tiles.value, max_r.value
+        self.table = host.to(self.dev, non_blocking=True)
+        self._host = host              # pinned source of the async copy: keep it until the plan dies
+        self.bytes = sum(2 * wi.numel() * wi.element_size() + (u.numel() + d.numel()) * u.element_size()
+                         for wi, u, d in zip(wins, ups, downs))             # algorithmic HBM bytes of one run
+
+    def run(self, alpha):
+        with torch.cuda.device(self.dev):
+            rc = nat.lib().b200lora_merge_batch_run(nat.ptr(self.table), self.n, self.tiles, self.max_r, float(alpha),
+                                                    nat.dtype_code(self.wdt), nat.dtype_code(self.ldt),
+                                                    nat.stream_ptr(self.dev))
+        nat.check(rc, "b200lora_merge_batch_run")
+
+
+def merge_lora_weights(weights, ups, downs, alpha=1.0, inplace=False):
+    """`W_i + alpha * (up_i @ down_i).type(W_i.dtype)` for a whole list of matrices — the loop of
+    `weight_apply_lora` (reference lora.py:410-424) — in ONE launch per (device, weight dtype, LoRA dtype) group
+    (`MergePlan`: a device-side problem table and a persistent grid over all tiles of all matrices).
+    Returns new tensors (dtype/device of each weight), or writes through `weights` when `inplace`."""
+    nat.lib()
+    n = len(weights)
+    if not (len(ups) == n and len(downs) == n):
+        raise RuntimeError("merge: weights / ups / downs differ in length")
+    outs = [None] * n
+    groups = {}
+    with torch.no_grad():
+        staged = []
+        for i, (weight, up, down) in enumerate(zip(weights, ups, downs)):
+            home = weight.device
+            dev = home if weight.is_cuda else _cuda_device()
+            w = weight.detach().to(dev)
+            if not w.is_contiguous():
+                w = w.contiguous()
+            u = up.detach().to(dev).contiguous()
+            d = down.detach().to(dev).contiguous()
+            if d.dtype != u.dtype:
+                d = d.to(u.dtype)
+            if w.dim() != 2 or u.dim() != 2 or d.dim() != 2 or u.shape != (w.shape[0], u.shape[1]) \
+                    or d.shape != (u.shape[1], w.shape[1]):
+                raise RuntimeError(f"merge: shapes up {tuple(u.shape)} / down {tuple(d.shape)} do not "
+                                   f"match weight {tuple(w.shape)}")
+            same = inplace and w.data_ptr() == weight.data_ptr()
+            out = w if same else torch.empty_like(w)
+            staged.append((w, u, d, out, home, dev, same))
+            groups.setdefault((dev, w.dtype, u.dtype), []).append(i)
+        for idx in groups.values():
+            MergePlan([staged[i][0] for i in idx], [staged[i][3] for i in idx], [staged[i][1] for i in idx],
+                      [staged[i][2] for i in idx]).run(alpha)
+        for i, (w, u, d, out, home, dev, same) in enumerate(staged):
+            if inplace and not same:
+                weights[i].data.copy_(out)
+                outs[i] = weights[i]
+            else:
+                outs[i] = out if home == dev else out.to(home)
+    return outs
 
 
 def lora_abs_mean(up, down):

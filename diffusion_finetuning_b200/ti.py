@@ -137,9 +137,14 @@ class PlaceholderAdamW:
     """
 
     def __init__(self, rows: PlaceholderTokenRows, lr: float = 5e-4, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, clip_ti_decay: bool = True, target_norm: float = 0.4):
+                 weight_decay: float = 0.0, clip_ti_decay: bool = True, target_norm: float = 0.4,
+                 capturable: bool = False):
+        """`capturable`: the learning rate and the step count live in device memory (`param_groups[0]["lr"]` is a
+        one-element device tensor an LR schedule fills in place), so `step()` can sit in a captured CUDA graph."""
         self.rows = rows
-        self.param_groups = [{"params": [rows.rows], "lr": float(lr), "initial_lr": float(lr), "betas": tuple(betas),
+        self.capturable = bool(capturable)
+        lr_slot = torch.tensor(float(lr), dtype=torch.float32, device=rows.rows.device) if capturable else float(lr)
+        self.param_groups = [{"params": [rows.rows], "lr": lr_slot, "initial_lr": float(lr), "betas": tuple(betas),
                               "eps": float(eps), "weight_decay": float(weight_decay)}]
         self.clip_ti_decay = bool(clip_ti_decay)
         self.target_norm = float(target_norm)
@@ -148,6 +153,7 @@ class PlaceholderAdamW:
         self.exp_avg_sq = torch.zeros_like(p)
         self.norms = torch.zeros((2, p.shape[0]), dtype=torch.float32, device=p.device)   # [pre, post] per row
         self._step = 0
+        self.step_dev = torch.zeros(p.shape[0], dtype=torch.float32, device=p.device) if capturable else None
 
     def zero_grad(self, set_to_none: bool = False):
         g = self.rows.rows.grad
@@ -165,9 +171,15 @@ class PlaceholderAdamW:
             return
         nat.require_cuda(p, "PlaceholderAdamW.step")
         grp = self.param_groups[0]
-        lr = float(grp["lr"] if lr is None else lr)
+        lr_dev = None
+        if self.capturable and lr is None:
+            lr_dev = grp["lr"]                      # read by the kernel at run (replay) time
+            lr = 0.0
+            lam = 1.0 if self.clip_ti_decay else -1.0     # >= 0: the kernel derives min(1, 100·lr) itself
+        else:
+            lr = float(grp["lr"] if lr is None else lr)
+            lam = min(1.0, 100.0 * lr) if self.clip_ti_decay else -1.0
         self._step += 1
-        lam = min(1.0, 100.0 * lr) if self.clip_ti_decay else -1.0
         table = self.rows.embedding.weight
         if not table.is_contiguous() or not p.is_contiguous():
             raise RuntimeError("embedding table and master rows must be contiguous")
@@ -179,6 +191,7 @@ class PlaceholderAdamW:
                                             nat.ptr(self.exp_avg), nat.ptr(self.exp_avg_sq), self._step, lr,
                                             float(b1), float(b2), float(grp["eps"]), float(grp["weight_decay"]),
                                             float(lam), self.target_norm, nat.ptr(self.norms),
+                                            nat.ptr(lr_dev), nat.ptr(self.step_dev) if lr_dev is not None else None,
                                             nat.stream_ptr(p.device))
             nat.check(rc, "b200lora_ti_step")
         # both tensors were written through raw pointers: tell autograd (version-keyed caches, saved tensors)
@@ -186,11 +199,16 @@ class PlaceholderAdamW:
         torch.autograd.graph.increment_version(p)
 
     def state_dict(self):
-        return {"step": self._step, "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(),
-                "lr": self.param_groups[0]["lr"]}
+        step = int(self.step_dev[0].item()) if self.capturable else self._step
+        return {"step": step, "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(),
+                "lr": float(self.param_groups[0]["lr"])}
 
     def load_state_dict(self, sd):
         self._step = int(sd["step"])
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
-        self.param_groups[0]["lr"] = float(sd["lr"])
+        if self.capturable:
+            self.step_dev.fill_(float(sd["step"]))
+            self.param_groups[0]["lr"].fill_(float(sd["lr"]))
+        else:
+            self.param_groups[0]["lr"] = float(sd["lr"])

@@ -35,7 +35,8 @@ from . import lora as L
 # LR schedules — diffusers.optimization.get_scheduler (requirements.txt: diffusers>=0.9.0), used at
 # train_lora_dreambooth.py:741-747 and cli_lora_pti.py:659-664, 746-751.  All are LambdaLR factors.
 # --------------------------------------------------------------------------------------------
-def _schedule_factor(name: str, warmup: int, total: Optional[int], num_cycles: float = 0.5):
+def _schedule_factor(name: str, warmup: int, total: Optional[int], num_cycles: float = 0.5, power: float = 1.0,
+                     lr_init: Optional[float] = None, lr_end: float = 1e-7):
     def ramp(step):
         return float(step) / float(max(1, warmup))
 
@@ -55,9 +56,33 @@ def _schedule_factor(name: str, warmup: int, total: Optional[int], num_cycles: f
             progress = float(step - warmup) / float(max(1, total - warmup))
             return max(0.0, 0.5 * (1.0 + math.cos(math.pi * float(num_cycles) * 2.0 * progress)))
         return f
-    if name in ("polynomial", "cosine_with_restarts"):
-        raise ValueError(f"{name} is a diffusers schedule this driver does not offer "
-                         "(constant, constant_with_warmup, linear, cosine)")
+    if name == "cosine_with_restarts":
+        # diffusers get_cosine_with_hard_restarts_schedule_with_warmup (default num_cycles = 1 there)
+        def f(step):
+            if step < warmup:
+                return ramp(step)
+            progress = float(step - warmup) / float(max(1, total - warmup))
+            if progress >= 1.0:
+                return 0.0
+            return max(0.0, 0.5 * (1.0 + math.cos(math.pi * ((float(num_cycles) * progress) % 1.0))))
+        return f
+    if name == "polynomial":
+        # diffusers get_polynomial_decay_schedule_with_warmup: the factor depends on the optimizer's initial lr
+        if lr_init is None:
+            raise ValueError("polynomial needs the initial learning rate (lr_init)")
+        if not lr_init > lr_end:
+            raise ValueError(f"lr_end ({lr_end}) must be be smaller than initial lr ({lr_init})")
+
+        def f(step):
+            if step < warmup:
+                return ramp(step)
+            if step > total:
+                return lr_end / lr_init
+            lr_range = lr_init - lr_end
+            decay_steps = total - warmup
+            pct_remaining = 1 - (step - warmup) / decay_steps
+            return (lr_range * pct_remaining ** power + lr_end) / lr_init
+        return f
     raise ValueError(f"{name} is not a valid SchedulerType")
 
 
@@ -101,9 +126,19 @@ class LambdaSchedule:
 
 
 def get_scheduler(name, optimizer, num_warmup_steps: int = 0, num_training_steps: Optional[int] = None,
-                  num_cycles: float = 0.5):
-    return LambdaSchedule(optimizer, _schedule_factor(str(name), int(num_warmup_steps or 0), num_training_steps,
-                                                      num_cycles))
+                  num_cycles: Optional[float] = None, power: float = 1.0):
+    """`diffusers.optimization.get_scheduler`: every schedule name it accepts.  `num_cycles` defaults to diffusers'
+    own per-schedule default (0.5 for cosine, 1 for cosine_with_restarts)."""
+    name = str(name)
+    if num_cycles is None:
+        num_cycles = 1 if name == "cosine_with_restarts" else 0.5
+    lr_init = None
+    if name == "polynomial":        # diffusers reads optimizer.defaults["lr"]; here: the first group's initial lr
+        g0 = optimizer.param_groups[0]
+        lr0 = g0.get("initial_lr", g0["lr"])
+        lr_init = float(lr0.item()) if torch.is_tensor(lr0) else float(lr0)
+    return LambdaSchedule(optimizer, _schedule_factor(name, int(num_warmup_steps or 0), num_training_steps,
+                                                      num_cycles, power, lr_init))
 
 
 # --------------------------------------------------------------------------------------------
@@ -160,6 +195,38 @@ def denoising_loss(model_pred, target, with_prior_preservation=False, prior_loss
     return loss + prior_loss_weight * prior_loss
 
 
+class LossScaler:
+    """Dynamic loss scaling for fp16 autocast over the flat gradient arena — `torch.cuda.amp.GradScaler` with its
+    defaults (init 2**16, growth 2 every 2000 clean steps, backoff 0.5), which is what accelerate puts around
+    `accelerator.backward` / `optimizer.step` for `--mixed_precision fp16`.  One pass over the arena unscales and
+    detects overflow; the host reads the flag (GradScaler.step does the same) and skips the update on overflow."""
+
+    def __init__(self, device, init_scale=65536.0, growth_factor=2.0, backoff_factor=0.5, growth_interval=2000):
+        self.scale_value = float(init_scale)
+        self.growth_factor, self.backoff_factor, self.growth_interval = growth_factor, backoff_factor, growth_interval
+        self._good = 0
+        self.skipped = 0
+
+    def scale(self, loss):
+        return loss * self.scale_value
+
+    def unscale_(self, arena) -> bool:
+        """Divide the (exchanged) gradients by the scale; False if any is non-finite (step must be skipped)."""
+        flat = arena.flat
+        flat.mul_(1.0 / self.scale_value)
+        ok = bool(torch.isfinite(flat).all().item())
+        if ok:
+            self._good += 1
+            if self._good >= self.growth_interval:
+                self.scale_value *= self.growth_factor
+                self._good = 0
+        else:
+            self.scale_value *= self.backoff_factor
+            self._good = 0
+            self.skipped += 1
+        return ok
+
+
 # --------------------------------------------------------------------------------------------
 # the driver
 # --------------------------------------------------------------------------------------------
@@ -191,6 +258,8 @@ class TrainConfig:
     learning_rate_ti: Optional[float] = None     # continue_inversion_lr / ti_lr (cli_lora_pti.py:715-722)
     clip_ti_decay: bool = False                  # perform_tuning has no norm decay; train_inversion has (:317)
     arena_optimizer: bool = False                # clip + AdamW over the flat arenas in one C-ABI call (dp.ArenaAdamW)
+    unet_targets: Optional[tuple] = None         # class names the UNet was injected under (None = discover every layer)
+    text_targets: Optional[tuple] = None
 
 
 class LoraTrainer:
@@ -244,15 +313,17 @@ class LoraTrainer:
             self.ti_opt = ti.PlaceholderAdamW(
                 placeholder_rows, lr=cfg.learning_rate if cfg.learning_rate_ti is None else cfg.learning_rate_ti,
                 betas=(cfg.adam_beta1, cfg.adam_beta2), eps=cfg.adam_epsilon, weight_decay=cfg.adam_weight_decay,
-                clip_ti_decay=cfg.clip_ti_decay)
+                clip_ti_decay=cfg.clip_ti_decay,
+                capturable=bool(cfg.use_cuda_graph and cfg.gradient_accumulation_steps == 1
+                                and cfg.mixed_precision != "fp16" and placeholder_rows.rows.is_cuda))
         self.arena = dp.LoraGradArena(holder, extra_params=arena_extra, bucket_bytes=cfg.bucket_bytes,
                                       process_group=process_group)
         self.arena.broadcast_params(0)
         self.device = self.arena.device
         on_cuda = self.device.type == "cuda"
-        # (the placeholder-row update takes lr and step as launch arguments: not replayable)
+        # fp16 runs dynamic loss scaling, whose skip-on-overflow is a host decision: not replayable
         self.graph_ok = bool(cfg.use_cuda_graph and on_cuda and cfg.gradient_accumulation_steps == 1
-                             and self.ti_opt is None)
+                             and cfg.mixed_precision != "fp16")
         opt_kw = dict(lr=cfg.learning_rate, betas=(cfg.adam_beta1, cfg.adam_beta2), weight_decay=cfg.adam_weight_decay,
                       eps=cfg.adam_epsilon)
         if on_cuda:
@@ -281,7 +352,11 @@ class LoraTrainer:
         if self.ti_opt is not None:             # one schedule over every group, as lr_scheduler_lora (:746-751)
             sched_target = argparse.Namespace(param_groups=(self.optimizer.param_groups if self.optimizer else [])
                                               + self.ti_opt.param_groups)
-        self.lr_scheduler = get_scheduler(cfg.lr_scheduler, sched_target, cfg.lr_warmup_steps, cfg.max_train_steps)
+        # the schedule is stepped once per loop iteration (micro-batch), so its horizon is in iterations:
+        # warm-up and total are multiplied by the accumulation factor (train_lora_dreambooth.py:737-742)
+        accum = max(1, cfg.gradient_accumulation_steps)
+        self.lr_scheduler = get_scheduler(cfg.lr_scheduler, sched_target, cfg.lr_warmup_steps * accum,
+                                          cfg.max_train_steps * accum)
         self.global_step = 0          # counts loop iterations, as the reference's does (:891)
         self.last_save = 0
         self._micro = 0
@@ -290,6 +365,9 @@ class LoraTrainer:
         if cfg.seed is not None:
             self._gen = torch.Generator(device=self.device).manual_seed(cfg.seed + self.rank)
         self.autocast_dtype = {"no": None, "fp16": torch.float16, "bf16": torch.bfloat16}[cfg.mixed_precision]
+        # accelerate wraps fp16 runs in a GradScaler (accelerator.backward / optimizer.step,
+        # train_lora_dreambooth.py:877-887): without it fp16 activation gradients underflow to zero silently
+        self.scaler = LossScaler(self.device) if (cfg.mixed_precision == "fp16" and on_cuda) else None
 
     # ------------------------------------------------------------------ loss
     def prepare(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
@@ -326,6 +404,8 @@ class LoraTrainer:
     def _update(self):
         cfg = self.cfg
         self.arena.finish()
+        if self.scaler is not None and not self.scaler.unscale_(self.arena):
+            return                       # overflow: the step is skipped and the scale backs off (GradScaler.step)
         if cfg.max_grad_norm is not None and cfg.max_grad_norm > 0 and not cfg.arena_optimizer:
             self.arena.clip_grad_norm_(cfg.max_grad_norm)      # (ArenaAdamW clips inside its own launch)
         if self.optimizer is not None:
@@ -333,10 +413,13 @@ class LoraTrainer:
         if self.ti_opt is not None:
             self.ti_opt.step()
 
+    def _backward(self, loss):
+        (loss if self.scaler is None else self.scaler.scale(loss)).backward()
+
     def _whole_step(self, b):
         self.arena.zero()
         loss = self.loss_fn(b)
-        loss.backward()
+        self._backward(loss)
         self._update()
         return loss
 
@@ -345,6 +428,21 @@ class LoraTrainer:
         optimizer state, library workspaces); a training job must not see those updates, so parameters and
         optimizer state are put back IN PLACE afterwards (the graph holds their addresses)."""
         params = self.arena.params
+        ti_keep = None
+        if self.ti_opt is not None:
+            tio = self.ti_opt
+            table = tio.rows.embedding.weight
+            ti_state = [tio.exp_avg, tio.exp_avg_sq, tio.step_dev, tio.rows.rows.data]
+            ti_keep = ([t.clone() for t in ti_state], table.detach()[tio.rows.row_ids].clone())
+
+        def restore_ti():
+            if ti_keep is None:
+                return
+            with torch.no_grad():
+                for t, k in zip(ti_state, ti_keep[0]):
+                    t.copy_(k)
+                table.data[tio.rows.row_ids] = ti_keep[1]
+
         if isinstance(self.optimizer, dp.ArenaAdamW):
             o = self.optimizer
             keep = [t.clone() for t in (o.flat_p, o.exp_avg, o.exp_avg_sq, o.scratch)]
@@ -352,18 +450,21 @@ class LoraTrainer:
             with torch.no_grad():
                 for t, k in zip((o.flat_p, o.exp_avg, o.exp_avg_sq, o.scratch), keep):
                     t.copy_(k)
+            restore_ti()
             return graphed
         saved_p = [p.detach().clone() for p in params]
-        saved_s = {id(p): {k: v.clone() for k, v in self.optimizer.state[p].items() if torch.is_tensor(v)}
-                   for p in params if p in self.optimizer.state}
+        opt_state = self.optimizer.state if self.optimizer is not None else {}
+        saved_s = {id(p): {k: v.clone() for k, v in opt_state[p].items() if torch.is_tensor(v)}
+                   for p in params if p in opt_state}
         graphed = dp.GraphedStep(self._whole_step, b)
         with torch.no_grad():
             for p, keep in zip(params, saved_p):
                 p.copy_(keep)
                 old = saved_s.get(id(p))
-                for k, v in self.optimizer.state.get(p, {}).items():
+                for k, v in opt_state.get(p, {}).items():
                     if torch.is_tensor(v):
                         v.copy_(old[k]) if old is not None else v.zero_()
+        restore_ti()
         return graphed
 
     def train_step(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
@@ -385,12 +486,12 @@ class LoraTrainer:
             last = self._micro == accum - 1
             if last:
                 loss = self.loss_fn(b) / accum
-                loss.backward()
+                self._backward(loss)
                 self._update()
             else:
                 with self.arena.no_sync():
                     loss = self.loss_fn(b) / accum
-                    loss.backward()
+                    self._backward(loss)
             self._micro = 0 if last else self._micro + 1
         if not cfg.scheduler_first:
             self.lr_scheduler.step()
@@ -402,12 +503,29 @@ class LoraTrainer:
         return self._micro == 0
 
     # ------------------------------------------------------------------ artefacts (rank 0)
+    def _targets(self, model, configured, default):
+        """The class names `model` was injected under: TrainConfig, else what `inject_trainable_lora*` recorded on
+        the model, else the reference's default.  Every injected layer must be reachable from them — a layer the
+        walk misses would be silently absent from the checkpoint."""
+        targets = set(configured) if configured else set(getattr(model, "_lora_injected_targets", None) or default)
+        injected = (L.LoraInjectedLinear, L.LoraInjectedConv2d)
+        have = sum(1 for m in model.modules() if isinstance(m, injected))
+        seen = {id(m) for _, _, m in L._find_modules(model, targets, search_class=list(injected))}
+        if len(seen) != have:
+            raise ValueError(f"{have - len(seen)} injected LoRA layer(s) are not under the target classes "
+                             f"{sorted(targets)}: set TrainConfig.unet_targets / text_targets to the set the model "
+                             "was injected with, or the checkpoint would miss them")
+        return targets
+
     def _save(self, unet_path, text_path=None):
         if self.optimizer is None:              # inversion phase: nothing but the rows; the caller saves those
             return
-        L.save_lora_weight(self.unet, unet_path)
+        L.save_lora_weight(self.unet, unet_path,
+                           target_replace_module=self._targets(self.unet, self.cfg.unet_targets, L.DEFAULT_TARGET_REPLACE))
         if self.cfg.train_text_encoder and text_path:
-            L.save_lora_weight(self.text_encoder, text_path, target_replace_module=["CLIPAttention"])
+            L.save_lora_weight(self.text_encoder, text_path,
+                               target_replace_module=self._targets(self.text_encoder, self.cfg.text_targets,
+                                                                   L.TEXT_ENCODER_DEFAULT_TARGET_REPLACE))
 
     def maybe_save(self, epoch: int):
         """Cadence and names of train_lora_dreambooth.py:893-958."""
@@ -435,9 +553,10 @@ class LoraTrainer:
         if cfg.output_format in ("pt", "both"):
             self._save(cfg.output_dir + "/lora_weight.pt", cfg.output_dir + "/lora_weight.text_encoder.pt")
         if cfg.output_format in ("safe", "both") and self.optimizer is not None:
-            loras = {"unet": (self.unet, {"CrossAttention", "Attention", "GEGLU"})}
+            loras = {"unet": (self.unet, self._targets(self.unet, cfg.unet_targets, L.DEFAULT_TARGET_REPLACE))}
             if cfg.train_text_encoder:
-                loras["text_encoder"] = (self.text_encoder, {"CLIPAttention"})
+                loras["text_encoder"] = (self.text_encoder, self._targets(self.text_encoder, cfg.text_targets,
+                                                                          L.TEXT_ENCODER_DEFAULT_TARGET_REPLACE))
             L.save_safeloras(loras, cfg.output_dir + "/lora_weight.safetensors")
 
     def fit(self, batches_per_epoch: Callable[[int], Iterable[Dict[str, torch.Tensor]]], on_log: Optional[Callable] = None):
@@ -497,6 +616,9 @@ def main(argv=None):
     from .fused import fuse_sibling_projections
     from .unet_sd15 import UNet2DConditionModel
     cfg = TrainConfig(**{f.name: getattr(a, f.name) for f in dataclasses.fields(TrainConfig)})
+    if a.extended and cfg.mixed_precision == "no":
+        raise SystemExit("--extended wraps the resnet convs in LoraInjectedConv2d, whose tensor-core path is 16-bit: "
+                         "run it with --mixed-precision bf16 (or fp16)")
     torch.manual_seed(0)
     unet = (UNet2DConditionModel.tiny() if a.tiny else UNet2DConditionModel()).to(device)
     unet.requires_grad_(False)
@@ -531,22 +653,20 @@ def main(argv=None):
     if tr.rank == 0 and steps > marks.get("s0", steps):
         ms = t0.elapsed_time(t1) / (steps - marks["s0"])
         print(f"{ms:.2f} ms/step, {a.train_batch_size * world / ms * 1e3:.1f} samples/s on {world} GPU(s)")
-    # A captured step holds NCCL work: drop the graph and let every rank finish before anything is torn down
-    # (a communicator destroyed under a live graph can block at exit; bench.py leaves the same way).
+    # A captured step holds NCCL work: drop the graph FIRST, drain the device, let every rank arrive, then
+    # destroy the process group and return — a communicator destroyed under a live graph blocks at exit.
+    import gc
     tr._graphed = None
+    tr.arena.detach()
+    gc.collect()
     torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
+        torch.cuda.synchronize(device)
+        dist.destroy_process_group()
     return 0
 
 
-def _leave(rc):
-    """Exit without interpreter teardown: communicators and graphs are process-lifetime objects here."""
-    import sys
-    sys.stdout.flush()
-    sys.stderr.flush()
-    os._exit(int(rc or 0))
-
-
 if __name__ == "__main__":
-    _leave(main())
+    import sys
+    sys.exit(main())

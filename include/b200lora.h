@@ -63,6 +63,19 @@ const char* b200lora_last_error(void);
 int b200lora_tc_supported(void);
 
 /*
+ * Diagnostics (not part of the drop-in surface; used by tools/ and by B200LORA_DEBUG_ERR=1):
+ *   b200lora_watchdog_code    non-zero after a tensor-core kernel's bounded barrier wait gave up:
+ *                             0x80000000 | wait-site << 16 | block index (every mbarrier wait in the tcgen05
+ *                             kernels is bounded so a protocol bug traps instead of wedging the GPU).
+ *   b200lora_peek_cuda_error  the CUDA runtime's pending error code, without clearing it.
+ *   b200lora_debug_timeline   `buf` = device buffer of 6*256 int64: the next tcgen05 launches record a clock64
+ *                             timeline of CTA `cta` into it (tools/timeline.py); NULL switches it off.
+ */
+unsigned int b200lora_watchdog_code(void);
+int b200lora_peek_cuda_error(void);
+void b200lora_debug_timeline(void* buf, int cta);
+
+/*
  * The generic fused kernel behind forward and backward-dX:
  *
  *     T = X · S1ᵀ                       [M, r]   (optionally written to T_out)
@@ -269,7 +282,10 @@ int b200lora_flat_axpby(const void* a, const void* b, void* out, int64_t n, floa
  *                          (lambda_ = min(1, 100 * lr), target_norm = 0.4 in the reference; lambda_ < 0 skips
  *                          the decay = clip_ti_decay False); then table[rows[p], :] = master_rows[p, :] cast to
  *                          table_dtype.  norms_out (nullable) [2, P] fp32: row norms before and after the decay
- *                          (the reference prints both).
+ *                          (the reference prints both).  Replayable form (the call sits in a captured CUDA
+ *                          graph): lr_dev (nullable) points at ONE device float that overrides `lr` (and, when
+ *                          lambda_ >= 0, lambda_ becomes min(1, 100 * lr_dev[0])); step_dev (nullable) [P] device
+ *                          floats hold the per-row step count, read as step = step_dev[p] + 1 and written back.
  */
 int b200lora_ti_grad_rows(const void* dY, const int64_t* token_ids, int64_t n_tokens, int D,
                           const int64_t* rows, int P, float* grad_rows, int io_dtype,
@@ -277,7 +293,8 @@ int b200lora_ti_grad_rows(const void* dY, const int64_t* token_ids, int64_t n_to
 int b200lora_ti_step(void* table, int table_dtype, int D, const int64_t* rows, int P, float* master_rows,
                      const float* grad_rows, float* exp_avg, float* exp_avg_sq, int step, float lr,
                      float beta1, float beta2, float eps, float weight_decay, float lambda_,
-                     float target_norm, float* norms_out, b200lora_stream_t stream);
+                     float target_norm, float* norms_out, const float* lr_dev, float* step_dev,
+                     b200lora_stream_t stream);
 
 /*
  * Weight merge — replaces lora.py:423  `weight + alpha * (up @ down).type(weight.dtype)`
@@ -288,6 +305,29 @@ int b200lora_ti_step(void* table, int table_dtype, int D, const int64_t* rows, i
 int b200lora_merge(const void* Win, void* Wout, const void* up, const void* down,
                    float alpha, int N, int K, int r, int w_dtype, int lora_dtype,
                    b200lora_stream_t stream);
+
+/*
+ * The same merge for MANY matrices in ONE launch — replaces the per-layer loop of lora.py:410-424
+ * (`weight_apply_lora`: 144 UNet + 48 text-encoder matrices in cli_lora_add.py:72-110).  All weights share w_dtype,
+ * all factors share lora_dtype, ranks may differ per item; same rounding as b200lora_merge; Wout may alias Win.
+ *   b200lora_merge_batch_plan  host only: validates `items` (a HOST array) and writes the device-format problem
+ *                              table (b200lora_merge_batch_workspace(n_items) bytes) into HOST memory `table_host`;
+ *                              returns the tile count and the largest rank the launch has to cover.
+ *   b200lora_merge_batch_run   one launch over the table, which the caller has copied to DEVICE memory (any way it
+ *                              likes; the table can be kept and re-run, e.g. for a sweep over alpha).
+ */
+typedef struct b200lora_merge_item {
+  const void* Win;
+  void* Wout;
+  const void* up;      /* [N, r] */
+  const void* down;    /* [r, K] */
+  int32_t N, K, r, reserved;
+} b200lora_merge_item;
+int64_t b200lora_merge_batch_workspace(int n_items);
+int b200lora_merge_batch_plan(const b200lora_merge_item* items, int n_items, int w_dtype, void* table_host,
+                              int64_t table_bytes, int64_t* total_tiles, int* max_rank);
+int b200lora_merge_batch_run(const void* table_dev, int n_items, int64_t total_tiles, int max_rank, float alpha,
+                             int w_dtype, int lora_dtype, b200lora_stream_t stream);
 
 /*
  * mean(|up @ down|) for one layer — replaces lora.py:744-746 (inspect_lora "moved" metric).

@@ -191,7 +191,153 @@ def golden_svd_fixture():
         json.dump(digest, fh, indent=1, sort_keys=True)
 
 
+# -------------------------------------------------------------------------------------------------
+# Rows A12 / N3 / N4: the reference's CLI modules EXECUTED (oracle/ref_exec.py stands in for their
+# diffusers / fire / wandb imports; the arithmetic that runs is the reference's own, unmodified)
+# -------------------------------------------------------------------------------------------------
+class _StandIn:
+    """Small pipeline stand-ins whose block classes carry the names the reference matches on."""
+
+    class CrossAttention(nn.Module):
+        def __init__(self, d, ctx):
+            super().__init__()
+            self.to_q = nn.Linear(d, d, bias=False)
+            self.to_k = nn.Linear(ctx, d, bias=False)
+            self.to_out = nn.ModuleList([nn.Linear(d, d)])
+
+    class GEGLU(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.proj = nn.Linear(d, 4 * d)
+
+    class CLIPAttention(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.q_proj = nn.Linear(d, d)
+            self.out_proj = nn.Linear(d, d)
+
+    class Pipe:
+        def __init__(self, seed, delta_seed=None):
+            torch.manual_seed(seed)
+            self.unet = nn.Sequential(_StandIn.CrossAttention(48, 40), _StandIn.GEGLU(48))
+            self.text_encoder = nn.Sequential(_StandIn.CLIPAttention(32))
+            if delta_seed is not None:           # "tuned" = base + a rank-3 update + small noise, per Linear
+                g = torch.Generator().manual_seed(delta_seed)
+                with torch.no_grad():
+                    for m in list(self.unet.modules()) + list(self.text_encoder.modules()):
+                        if isinstance(m, nn.Linear):
+                            N, K = m.weight.shape
+                            m.weight += (torch.randn(N, 3, generator=g) * 0.05) @ (torch.randn(3, K, generator=g) * 0.3) \
+                                + 1e-3 * torch.randn(N, K, generator=g)
+            self.unet.half()
+            self.text_encoder.half()
+
+        def to(self, *_a, **_k):
+            return self
+
+
+def golden_svd_distill(tmp):
+    """cli_svd.svd_distill (cli_svd.py:29-111) run on two stand-in fp16 pipelines, on the CPU."""
+    from oracle import ref_exec
+    pipes = {"base": _StandIn.Pipe(21), "tuned": _StandIn.Pipe(21, delta_seed=22)}
+    cli, _ = ref_exec.load_cli("cli_svd", pipeline_factory=lambda path, **kw: pipes[path])
+    out = os.path.join(tmp, "svd_distill.pt")
+    cli.svd_distill("tuned", "base", rank=4, clamp_quantile=0.99, device="cpu", save_path=out)
+    blob = {}
+    for which, model_of in (("unet", lambda p: p.unet), ("text", lambda p: p.text_encoder)):
+        targets = ["CrossAttention", "Attention", "GEGLU"] if which == "unet" else ["CLIPAttention"]
+        for tag in ("base", "tuned"):
+            for i, w in enumerate(cli.extract_linear_weights(model_of(pipes[tag]), targets)):
+                blob[f"{which}.{tag}.{i}"] = w.detach().clone()
+        path = out if which == "unet" else cli._text_lora_path(out)
+        for i, t in enumerate(torch.load(path)):
+            blob[f"{which}.out.{i}"] = t.detach().clone()
+    save_file({k: v.contiguous() for k, v in blob.items()}, os.path.join(OUT, "svd_distill_case.safetensors"),
+              {"rank": "4", "clamp_quantile": "0.99"})
+
+
+def golden_lpl(tmp):
+    """cli_lora_add.add(mode="lpl", with_text_lora=True) (cli_lora_add.py:17-71) on two fp16 `.pt` lists."""
+    from oracle import ref_exec
+    cli, _ = ref_exec.load_cli("cli_lora_add")
+    g = torch.Generator().manual_seed(31)
+    blob = {}
+    paths = {}
+    for tag in ("a", "b"):
+        for kind, shapes in (("unet", [(48, 4), (4, 48), (192, 4), (4, 48), (48, 1), (1, 40)]),
+                             ("text", [(32, 4), (4, 32), (32, 4), (4, 32)])):
+            lst = [(torch.randn(s, generator=g) * 0.1).half() for s in shapes]
+            p = os.path.join(tmp, f"{tag}.pt" if kind == "unet" else f"{tag}.text_encoder.pt")
+            torch.save(lst, p)
+            paths[(tag, kind)] = p
+            for i, t in enumerate(lst):
+                blob[f"{kind}.{tag}.{i}"] = t.clone()
+    out = os.path.join(tmp, "mix.pt")
+    cli.add(paths[("a", "unet")], paths[("b", "unet")], out, alpha=0.3, mode="lpl", with_text_lora=True)
+    for kind, p in (("unet", out), ("text", cli._text_lora_path(out))):
+        for i, t in enumerate(torch.load(p)):
+            blob[f"{kind}.out.{i}"] = t.detach().clone()
+    save_file({k: v.contiguous() for k, v in blob.items()}, os.path.join(OUT, "lpl_case.safetensors"), {"alpha": "0.3"})
+
+
+def golden_train_inversion(tmp):
+    """cli_lora_pti.train_inversion (cli_lora_pti.py:250-405) run for 6 steps on a stand-in text encoder: its own
+    optimizer recipe (:651-657), LambdaLR linear decay stepped first (:293), clip_ti_decay norm decay and the restore
+    of every non-placeholder row (:315-346).  Only `loss_step` (the UNet denoising loss, :196-247) is replaced, by a
+    quadratic loss over the embedded tokens, so the gradient rows are dense and known."""
+    from oracle import ref_exec
+    cli, _ = ref_exec.load_cli("cli_lora_pti")
+    V, D, T, B, steps = 60, 24, 9, 3, 6
+    rows = [57, 59]
+    torch.manual_seed(41)
+
+    class Text(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = nn.Embedding(V, D)
+
+        def get_input_embeddings(self):
+            return self.emb
+
+    class Unet(nn.Module):
+        pass
+
+    text = Text()
+    with torch.no_grad():
+        text.emb.weight.mul_(0.3)
+    g = torch.Generator().manual_seed(42)
+    batches = []
+    for _ in range(steps):
+        ids = torch.randint(0, V - 3, (B, T), generator=g)
+        ids[:, 2], ids[:, 5] = rows[0], rows[1]
+        ids[0, 7] = rows[1]
+        batches.append({"input_ids": ids, "w": torch.randn(B, T, D, generator=g), "y": torch.randn(B, T, generator=g)})
+
+    def loss_step(batch, unet, vae, text_encoder, scheduler, mixed_precision=False, **_kw):
+        e = text_encoder.get_input_embeddings()(batch["input_ids"])
+        return ((e * batch["w"]).sum(-1) - batch["y"]).pow(2).mean()
+
+    cli.loss_step = loss_step
+    table0 = text.emb.weight.detach().clone()
+    index_no_updates = torch.ones(V, dtype=torch.bool)
+    index_no_updates[rows] = False
+    lr, wd = 5e-3, 1e-2
+    opt = torch.optim.AdamW(text.get_input_embeddings().parameters(), lr=lr, betas=(0.9, 0.999), eps=1e-08,
+                            weight_decay=wd)
+    total = 8
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: max(0.0, (total - s) / total))    # diffusers "linear", no warm-up
+    cli.train_inversion(Unet(), None, text, batches, steps, None, index_no_updates, opt, 10 ** 9, rows, ["<a>", "<b>"],
+                        tmp, None, sched, tmp, accum_iter=1, log_wandb=False, mixed_precision=False, clip_ti_decay=True)
+    blob = {"table0": table0, "table_final": text.emb.weight.detach().clone(), "rows": torch.tensor(rows)}
+    for i, b in enumerate(batches):
+        for k, v in b.items():
+            blob[f"b{i}.{k}"] = v
+    save_file({k: v.contiguous() for k, v in blob.items()}, os.path.join(OUT, "train_inversion_case.safetensors"),
+              {"lr": str(lr), "weight_decay": str(wd), "steps": str(steps), "sched_total": str(total)})
+
+
 def main():
+    import tempfile
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
     golden_linear(ref)
@@ -199,6 +345,10 @@ def main():
     golden_safeloras_fixture(ref)
     golden_merge(ref)
     golden_svd_fixture()
+    with tempfile.TemporaryDirectory() as tmp:
+        golden_svd_distill(tmp)
+        golden_lpl(tmp)
+        golden_train_inversion(tmp)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -130,3 +130,106 @@ def test_arena_layout_and_low_precision_params():
     # every parameter got a disjoint slice, in reverse module order
     offs = sorted(arena._slot.values())
     assert offs[0][0] == 0 and all(a[0] + a[1] == b[0] for a, b in zip(offs, offs[1:]))
+
+
+# ---------------------------------------------------------------------------------------------------
+# GradSink protocol (ops.GradSink): the kernel adds into the arena and the Function returns NO gradient for
+# the factors; the arena's post-accumulate hook — once per backward per parameter, after every use of the
+# layer — is the only "slice final" signal.  A layer that runs TWICE in one step must be exchanged after its
+# LAST backward, and a sink layer must count once, not twice (round 1 signalled from the sink AND the hook:
+# buckets fired after half of their layers).
+# ---------------------------------------------------------------------------------------------------
+class _SinkLinear(torch.autograd.Function):
+    """What ops._LoraLinearFn does with a sink, with the oracle's math in place of the CUDA kernels."""
+    pending = {}        # id(module) -> backward calls still to come (test instrumentation)
+
+    @staticmethod
+    def forward(ctx, x, mod, A, B):
+        from oracle import lora_oracle as O
+        ctx.mod = mod
+        ctx.save_for_backward(x)
+        _SinkLinear.pending[id(mod)] = _SinkLinear.pending.get(id(mod), 0) + 1
+        return O.lora_linear_forward(x, mod.linear.weight, mod.linear.bias, A.detach(), B.detach(), mod.scale)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from oracle import lora_oracle as O
+        (x,) = ctx.saved_tensors
+        mod = ctx.mod
+        dx, dA, dB = O.lora_linear_grads(x, mod.linear.weight.detach(), None, mod.lora_down.weight.detach(),
+                                         mod.lora_up.weight.detach(), mod.scale, dy)
+        mod._grad_sink.dA.add_(dA)
+        mod._grad_sink.dB.add_(dB)
+        _SinkLinear.pending[id(mod)] -= 1
+        return dx, None, None, None
+
+
+def _layers(m):
+    import diffusion_finetuning_b200 as L
+    return [mod for mod in m.modules() if isinstance(mod, L.LoraInjectedLinear)]
+
+
+def _loss_twice(m, x, through_sink):
+    """every layer is applied TWICE (weights shared between the two uses)"""
+    from oracle import lora_oracle as O
+    h = x
+    for _ in range(2):
+        for mod in _layers(m):
+            if through_sink:
+                h = torch.tanh(_SinkLinear.apply(h, mod, mod.lora_down.weight, mod.lora_up.weight))
+            else:
+                h = torch.tanh(O.lora_linear_forward(h, mod.linear.weight, mod.linear.bias, mod.lora_down.weight,
+                                                     mod.lora_up.weight, mod.scale))
+    return (h ** 2).mean()
+
+
+def _worker_twice(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from diffusion_finetuning_b200 import dp
+        m = _model(seed=10 + rank)
+        arena = dp.LoraGradArena(m, bucket_bytes=2048)
+        assert len(arena.buckets) > 2
+        arena.broadcast_params(0)
+        early = []
+        orig_fire = arena._fire
+
+        def spy(b):
+            bi = arena.buckets.index(b)
+            for layer in _layers(m):
+                if arena._slot[id(layer.lora_up.weight)][2] == bi or arena._slot[id(layer.lora_down.weight)][2] == bi:
+                    early.append(_SinkLinear.pending.get(id(layer), 0) > 0)
+            return orig_fire(b)
+        arena._fire = spy
+        g = torch.Generator().manual_seed(7)
+        x_all = torch.randn(world * 4, 32, generator=g)
+        arena.zero()
+        x = x_all[rank * 4:(rank + 1) * 4].clone().requires_grad_(True)
+        _loss_twice(m, x, through_sink=True).backward()
+        fired_in_backward = sum(b.fired for b in arena.buckets)
+        arena.finish()
+        assert early and not any(early), "a bucket was exchanged while one of its layers still had a backward to run"
+        assert fired_in_backward == len(arena.buckets), "every bucket should fire from inside the backward"
+        got = arena.flat.clone()
+        if rank == 0:
+            torch.save({"got": got, "x": x_all, "state": {k: v.clone() for k, v in m.state_dict().items()}}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_layer_used_twice_per_step_is_exchanged_after_its_last_backward(tmp_path):
+    out = str(tmp_path / "twice.pt")
+    mp.spawn(_worker_twice, args=(2, _free_port(), out), nprocs=2, join=True)
+    blob = torch.load(out)
+    m = _model(seed=10)
+    m.load_state_dict(blob["state"])
+    params = [p for mod in reversed(_layers(m)) for p in (mod.lora_up.weight, mod.lora_down.weight)]
+    x = blob["x"]
+    loss = (_loss_twice(m, x[:4], False) + _loss_twice(m, x[4:], False)) / 2
+    grads = torch.autograd.grad(loss, params)
+    want = torch.cat([g.reshape(-1) for g in grads])
+    rel = (blob["got"] - want).norm() / want.norm()
+    assert rel < 1e-5, rel

@@ -114,3 +114,100 @@ def test_streamed_writers_equal_the_reference_layout_writers(arena_params, tmp_p
     assert fr.metadata() == fo.metadata() and sorted(fr.keys()) == sorted(fo.keys())
     for k in fr.keys():
         assert torch.equal(fr.get_tensor(k), fo.get_tensor(k))
+
+
+# ---------------------------------------------------------------------------------------------------
+# against fixtures the REFERENCE computed (oracle/make_golden.py executes cli_lora_add.add and cli_svd.svd_distill)
+# ---------------------------------------------------------------------------------------------------
+def _numbered(blob, prefix):
+    out = []
+    while f"{prefix}.{len(out)}" in blob:
+        out.append(blob[f"{prefix}.{len(out)}"])
+    return out
+
+
+def test_lpl_equals_reference_run_bit_for_bit(tmp_path):
+    from conftest import load_golden
+    blob, meta = load_golden("lpl_case.safetensors")
+    for kind, suffix in (("unet", ".pt"), ("text", ".text_encoder.pt")):
+        torch.save(_numbered(blob, f"{kind}.a"), tmp_path / f"a{suffix}")
+        torch.save(_numbered(blob, f"{kind}.b"), tmp_path / f"b{suffix}")
+    A.lora_add(str(tmp_path / "a.pt"), str(tmp_path / "b.pt"), str(tmp_path / "o.pt"), alpha=float(meta["alpha"]),
+               mode="lpl", with_text_lora=True)
+    for kind, suffix in (("unet", ".pt"), ("text", ".text_encoder.pt")):
+        got, want = torch.load(tmp_path / f"o{suffix}"), _numbered(blob, f"{kind}.out")
+        assert len(got) == len(want)
+        for a, b in zip(got, want):
+            assert a.dtype == b.dtype == torch.float16 and torch.equal(a, b)
+
+
+class _Pipes:
+    """Stand-in pipelines with the block class names cli_svd.py:46-54 matches on, filled from the fixture."""
+
+    class CrossAttention(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.to_q = torch.nn.Linear(48, 48, bias=False)
+            self.to_k = torch.nn.Linear(40, 48, bias=False)
+            self.to_out = torch.nn.ModuleList([torch.nn.Linear(48, 48)])
+
+    class GEGLU(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.proj = torch.nn.Linear(48, 192)
+
+    class CLIPAttention(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.q_proj = torch.nn.Linear(32, 32)
+            self.out_proj = torch.nn.Linear(32, 32)
+
+    class Pipe:
+        def __init__(self, blob, tag, device):
+            self.unet = torch.nn.Sequential(_Pipes.CrossAttention(), _Pipes.GEGLU()).half()
+            self.text_encoder = torch.nn.Sequential(_Pipes.CLIPAttention()).half()
+            for which, model, targets in (("unet", self.unet, A.SVD_UNET_TARGETS), ("text", self.text_encoder, A.SVD_TEXT_TARGETS)):
+                ws = A.extract_linear_weights(model, targets)
+                src = _numbered(blob, f"{which}.{tag}")
+                assert len(ws) == len(src)
+                with torch.no_grad():
+                    for w, s in zip(ws, src):
+                        w.copy_(s)
+            self.unet.to(device)
+            self.text_encoder.to(device)
+
+
+def _aligned(U, Vh, Ug, Vg):
+    """cuSOLVER and LAPACK pick the sign of each singular pair independently: flip ours onto the fixture's."""
+    sign = torch.sign((U * Ug).sum(0))
+    sign[sign == 0] = 1
+    return U * sign, Vh * sign[:, None]
+
+
+def test_svd_distill_end_to_end_against_reference_run(tmp_path):
+    """cli_svd.svd_distill (cli_svd.py:29-111): extraction order, fp16 difference, rank-4 factors, fp32 lists in
+    `save_path` and `<save_path>.text_encoder.pt`.  The clamp threshold is a quantile of the SIGNED entries, so it
+    depends on the SVD's sign choice: factors are compared after sign alignment on the entries strictly inside both
+    clamps, the products everywhere."""
+    from conftest import load_golden, rel_err
+    blob, meta = load_golden("svd_distill_case.safetensors")
+    pipes = {}
+    out = tmp_path / "svd_distill.pt"
+    got_unet, got_clip = A.svd_distill("tuned", "base", rank=int(meta["rank"]), clamp_quantile=float(meta["clamp_quantile"]),
+                                       device=DEV, save_path=str(out),
+                                       load_pipeline=lambda path, device: pipes.setdefault(path, _Pipes.Pipe(blob, path, device)))
+    for which, path, got_live in (("unet", out, got_unet), ("text", tmp_path / "svd_distill.text_encoder.pt", got_clip)):
+        got, want = torch.load(path), _numbered(blob, f"{which}.out")
+        assert len(got) == len(want) == len(got_live)
+        for i in range(0, len(want), 2):
+            U, Vh, Ug, Vg = got[i].float().cpu(), got[i + 1].float().cpu(), want[i], want[i + 1]
+            assert got[i].dtype == torch.float32 and U.shape == Ug.shape and Vh.shape == Vg.shape
+            U, Vh = _aligned(U, Vh, Ug, Vg)
+            hi = min(max(U.abs().max(), Vh.abs().max()), max(Ug.abs().max(), Vg.abs().max())).item()
+            for a, b in ((U, Ug), (Vh, Vg)):
+                inside = (a.abs() < 0.999 * hi) & (b.abs() < 0.999 * hi)
+                assert inside.float().mean() > 0.9
+                assert (a[inside] - b[inside]).abs().max().item() < 2e-4 * max(1.0, b.abs().max().item())
+            assert rel_err(U @ Vh, Ug @ Vg) < 2e-2              # differs only through which entries the clamp bites
+            delta = (blob[f"{which}.tuned.{i // 2}"] - blob[f"{which}.base.{i // 2}"]).float()
+            assert rel_err(U @ Vh, delta) < 0.15                # and it is a rank-4 approximation of tuned - base

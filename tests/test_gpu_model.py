@@ -72,6 +72,50 @@ def test_merge_kernel_shapes_and_dtypes(wdt):
         assert rel_err(got, want.float()) < (1e-6 if wdt == torch.float32 else 3e-3)
 
 
+@pytest.mark.parametrize("wdt,ldt", [(torch.float32, torch.float32), (torch.float16, torch.float16),
+                                     (torch.bfloat16, torch.bfloat16), (torch.float32, torch.float16),
+                                     (torch.float16, torch.float32)])
+def test_merge_batch_one_launch_equals_oracle_and_per_matrix_kernel(wdt, ldt):
+    """b200lora_merge_batch (every matrix of a model in ONE launch, lora.py:410-424) against the oracle's
+    lora.py:423 expression and, bit for bit, against the per-matrix kernel; ragged shapes (N not a multiple of the
+    64-row tile, K not a multiple of the 512-byte tile row), mixed ranks incl. r > 8 (two passes) in one call."""
+    from diffusion_finetuning_b200 import _native as nat
+    g = torch.Generator().manual_seed(11)
+    shapes = [(320, 320, 4), (1280, 1280, 4), (2560, 320, 4), (77, 768, 1), (320, 768, 16), (640, 2560, 8), (65, 264, 3)]
+    Ws = [(torch.randn(N, K, generator=g) * 0.03).to(wdt) for N, K, _ in shapes]
+    ups = [(torch.randn(N, r, generator=g) * 0.05).to(ldt) for N, _, r in shapes]
+    downs = [(torch.randn(r, K, generator=g) * 0.3).to(ldt) for _, K, r in shapes]
+    n0 = nat.LAUNCHES
+    got = ops.merge_lora_weights([w.to(DEV) for w in Ws], [u.to(DEV) for u in ups], [d.to(DEV) for d in downs], 0.6)
+    assert nat.LAUNCHES - n0 == 1
+    for w, u, d, y in zip(Ws, ups, downs, got):
+        want = O.merge_weight(w, u, d, 0.6)
+        assert y.dtype == wdt and y.shape == w.shape
+        tol = 1e-6 if wdt == torch.float32 and ldt == torch.float32 else 3e-3
+        assert rel_err(y, want.float()) < tol
+        assert (y.float().cpu() - want.float()).abs().max().item() <= (2e-7 if tol == 1e-6 else 2e-3)
+        single = ops.merge_lora_weight(w.to(DEV), u.to(DEV), d.to(DEV), 0.6)
+        assert torch.equal(single, y)
+    # in place: the weights themselves are updated, still one launch
+    dev_w = [w.to(DEV) for w in Ws]
+    ptrs = [w.data_ptr() for w in dev_w]
+    ops.merge_lora_weights(dev_w, [u.to(DEV) for u in ups], [d.to(DEV) for d in downs], 0.6, inplace=True)
+    assert [w.data_ptr() for w in dev_w] == ptrs and all(torch.equal(a, b) for a, b in zip(dev_w, got))
+
+
+def test_merge_batch_matches_reference_vectors():
+    blob, meta = load_golden("merge_cases.safetensors")
+    alpha = float(meta["alpha"])
+    for tag in ("f32", "f16"):
+        ws = [blob[f"{tag}.w_q"], blob[f"{tag}.w_o"]]
+        us = [blob[f"{tag}.lora0"], blob[f"{tag}.lora2"]]
+        ds = [blob[f"{tag}.lora1"], blob[f"{tag}.lora3"]]
+        got = ops.merge_lora_weights(ws, us, ds, alpha)           # host buffers staged through the GPU
+        for y, want in zip(got, (blob[f"{tag}.merged_q"], blob[f"{tag}.merged_o"])):
+            assert y.device.type == "cpu"
+            assert torch.allclose(y, want, rtol=0, atol=2e-7 if tag == "f32" else 1e-4), tag
+
+
 def test_weight_apply_lora_and_inspect_and_collapse():
     class CrossAttention(torch.nn.Module):
         def __init__(self):

@@ -130,3 +130,71 @@ def test_rows_join_the_gradient_arena():
     want = torch.tensor([[2.0], [1.0]], device=DEV).expand(2, 128)
     assert torch.equal(pr.rows.grad, want)
     assert pr.rows.grad.data_ptr() == arena.flat.data_ptr()
+
+
+def test_train_inversion_against_reference_run():
+    """The fixture is the REFERENCE's `cli_lora_pti.train_inversion` (cli_lora_pti.py:250-405) executed for 6 steps
+    (oracle/make_golden.py): dense AdamW (:651-657), linear LR decay stepped first (:293), norm decay and restore
+    (:315-346).  Here: PlaceholderTokenRows + PlaceholderAdamW on the GPU, same batches, same loss."""
+    from conftest import load_golden
+    blob, meta = load_golden("train_inversion_case.safetensors")
+    lr, wd, steps, total = float(meta["lr"]), float(meta["weight_decay"]), int(meta["steps"]), int(meta["sched_total"])
+    V, D = blob["table0"].shape
+    emb = nn.Embedding(V, D).to(DEV)
+    with torch.no_grad():
+        emb.weight.copy_(blob["table0"].to(DEV))
+    rows = blob["rows"].tolist()
+    pr = ti.PlaceholderTokenRows(emb, rows).install()
+    opt = ti.PlaceholderAdamW(pr, lr=lr, weight_decay=wd, clip_ti_decay=True)
+    for i in range(steps):
+        step_lr = lr * max(0.0, (total - (i + 1)) / total)          # scheduler stepped before the update
+        opt.param_groups[0]["lr"] = step_lr
+        e = emb(blob[f"b{i}.input_ids"].to(DEV))
+        loss = ((e * blob[f"b{i}.w"].to(DEV)).sum(-1) - blob[f"b{i}.y"].to(DEV)).pow(2).mean()
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+    got, want = emb.weight.detach().cpu(), blob["table_final"]
+    assert rel_err(got[rows], want[rows]) < 1e-5
+    assert (got[rows] - want[rows]).abs().max().item() < 1e-5
+    keep = torch.ones(V, dtype=torch.bool)
+    keep[rows] = False
+    assert torch.equal(got[keep], want[keep])
+
+
+def test_capturable_step_follows_device_lr_and_step_count():
+    """`capturable=True`: lr and the step count live on the device, so a captured launch keeps following an LR
+    schedule and the bias correction; 4 replays of ONE captured step == 4 eager steps with the same lr sequence."""
+    V, D, rows = 64, 96, [61, 63]
+    torch.manual_seed(0)
+    tables = [nn.Embedding(V, D).to(DEV) for _ in range(2)]
+    tables[1].load_state_dict(tables[0].state_dict())
+    prs = [ti.PlaceholderTokenRows(t, rows).install() for t in tables]
+    eager = ti.PlaceholderAdamW(prs[0], lr=1e-2, weight_decay=1e-2)
+    graphed = ti.PlaceholderAdamW(prs[1], lr=1e-2, weight_decay=1e-2, capturable=True)
+    g = torch.Generator().manual_seed(1)
+    grads = [torch.randn(len(rows), D, generator=g).to(DEV) for _ in range(4)]
+    lrs = [1e-2, 7e-3, 4e-3, 1e-3]
+    static_g = torch.zeros(len(rows), D, device=DEV)
+    prs[1].rows.grad = static_g
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            graphed.step()
+    torch.cuda.current_stream().wait_stream(side)
+    # the capture itself launched nothing: state untouched
+    assert graphed.step_dev.abs().sum().item() == 0
+    for gi, lr in zip(grads, lrs):
+        prs[0].rows.grad = gi.clone()
+        eager.step(lr=lr)
+        static_g.copy_(gi)
+        graphed.param_groups[0]["lr"].fill_(lr)
+        graph.replay()
+    torch.cuda.synchronize()
+    assert graphed.step_dev.tolist() == [4.0, 4.0]
+    # (lambda = min(1, 100·lr) is formed in double on the host for the eager step and in fp32 inside the kernel for
+    # the replayed one: one ulp apart at most)
+    assert torch.allclose(prs[0].rows.detach(), prs[1].rows.detach(), rtol=1e-6, atol=1e-7)
+    assert torch.allclose(tables[0].weight.detach(), tables[1].weight.detach(), rtol=1e-6, atol=1e-7)

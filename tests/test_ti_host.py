@@ -35,7 +35,7 @@ def test_c_abi_argument_checks_without_gpu():
     lib = nat.lib()
     assert lib.b200lora_ti_grad_rows(None, None, 0, 8, None, 1, None, nat.F32, None) == -6
     assert lib.b200lora_ti_step(None, 0, 8, None, 1, None, None, None, None, 1, 1e-3, 0.9, 0.999, 1e-8, 0.0, 0.1,
-                                0.4, None, None) == -6
+                                0.4, None, None, None, None) == -6
 
 
 def test_oracle_post_step_properties():

@@ -165,9 +165,10 @@ def test_loop_dp2_equals_single_process(tmp_path):
     for a, b in zip(_lora_state(m), r0["state"]):
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-7)
     assert r0["lr"] == pytest.approx(tr.lr_scheduler.get_last_lr())
-    # schedule: one LambdaLR step per loop iteration (train_lora_dreambooth.py:886), linear warmup 2 of 8
-    assert [round(lr / 1e-2, 6) for _, lr in seen] == [0.5, 1.0, round(5 / 6, 6), round(4 / 6, 6), 0.5, round(2 / 6, 6),
-                                                       round(1 / 6, 6), 0.0]
+    # schedule: one LambdaLR step per loop iteration (train_lora_dreambooth.py:886); its horizon is in iterations:
+    # warm-up 2 x accumulation 2 = 4 of 8 x 2 = 16 (:737-742), of which the loop runs max_train_steps = 8 (:963)
+    assert [round(lr / 1e-2, 6) for _, lr in seen] == [0.25, 0.5, 0.75, 1.0, round(11 / 12, 6), round(10 / 12, 6),
+                                                       0.75, round(8 / 12, 6)]
     # save cadence and names (train_lora_dreambooth.py:893-958, 966-993): rank 0 only
     for d in (out, solo):
         names = sorted(n for n in os.listdir(d) if n.startswith("lora_weight"))
@@ -200,3 +201,73 @@ def test_accumulation_equals_big_batch_and_clip_bites(tmp_path):
     assert all(n <= 0.05 * (1 + 1e-5) for n in norms) and max(norms) > 0.049      # the clip was active
     with pytest.raises(ValueError):
         T.LoraTrainer(nn.Linear(4, 4), _cfg(str(tmp_path / "c")))                 # "No lora injected."
+
+
+def test_polynomial_and_cosine_with_restarts_follow_the_diffusers_definitions():
+    """diffusers.optimization: get_cosine_with_hard_restarts_schedule_with_warmup (num_cycles default 1) and
+    get_polynomial_decay_schedule_with_warmup (lr_end 1e-7, power 1) — closed forms, spot values."""
+    c = T._schedule_factor("cosine_with_restarts", 2, 12, num_cycles=2)
+    assert c(0) == 0.0 and c(1) == 0.5 and c(2) == 1.0                       # warm-up ramp, then the first cycle starts
+    assert abs(c(7) - 1.0) < 1e-12                                           # hard restart at the half-way point
+    assert abs(c(4) - 0.5 * (1 + math.cos(math.pi * 0.4))) < 1e-12 and c(12) == 0.0 and c(20) == 0.0
+    p = T._schedule_factor("polynomial", 2, 12, lr_init=1e-3)
+    assert p(1) == 0.5 and abs(p(2) - 1.0) < 1e-12 and abs(p(7) - (0.5 * (1e-3 - 1e-7) + 1e-7) / 1e-3) < 1e-12
+    assert abs(p(12) - 1e-4) < 1e-12 and p(13) == 1e-7 / 1e-3
+    w = torch.nn.Parameter(torch.zeros(3))
+    opt = torch.optim.SGD([w], lr=1e-3)
+    sched = T.get_scheduler("polynomial", opt, num_warmup_steps=2, num_training_steps=12)
+    for _ in range(12):
+        sched.step()
+    assert opt.param_groups[0]["lr"] == pytest.approx(1e-7)
+    sched = T.get_scheduler("cosine_with_restarts", torch.optim.SGD([w], lr=1e-3), 0, 10)    # diffusers default: 1 cycle
+    for _ in range(5):
+        sched.step()
+    assert sched.get_last_lr()[0] == pytest.approx(0.5e-3)
+    with pytest.raises(ValueError):
+        T.get_scheduler("polynomial", torch.optim.SGD([w], lr=1e-8), 0, 10)    # lr_end must be below the initial lr
+
+
+class ResnetBlock2D(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.conv1 = nn.Conv2d(c, c, 3, padding=1)
+        self.time_emb_proj = nn.Linear(8, c)
+
+
+def test_checkpoints_of_an_extended_injection_hold_every_trained_layer(tmp_path):
+    """inject_trainable_lora_extended adds layers under ResnetBlock2D; the savers must walk the set the model was
+    injected under (it is recorded on the model), or the conv / time_emb_proj LoRAs are silently dropped."""
+    import diffusion_finetuning_b200 as L
+    torch.manual_seed(0)
+    m = nn.Sequential(CrossAttention(16), ResnetBlock2D(16))
+    m.requires_grad_(False)
+    L.inject_trainable_lora_extended(m, r=2)
+    n_injected = sum(isinstance(x, (L.LoraInjectedLinear, L.LoraInjectedConv2d)) for x in m.modules())
+    assert n_injected == 6 and m._lora_injected_targets == L.UNET_EXTENDED_TARGET_REPLACE
+    with torch.no_grad():
+        for x in m.modules():
+            if isinstance(x, (L.LoraInjectedLinear, L.LoraInjectedConv2d)):
+                x.lora_up.weight.normal_(0, 0.05)
+    tr = T.LoraTrainer(m, _cfg(str(tmp_path), gradient_accumulation_steps=1), loss_fn=lambda b: None)
+    tr.save_final()
+    saved = torch.load(tmp_path / "lora_weight.pt")
+    assert len(saved) == 2 * n_injected
+    assert any(t.dim() == 4 for t in saved)                   # the conv LoRA is in the file
+    # round trip into a fresh model through the extended loader
+    torch.manual_seed(0)
+    fresh = nn.Sequential(CrossAttention(16), ResnetBlock2D(16))
+    L.monkeypatch_or_replace_lora_extended(fresh, [t.clone() for t in saved],
+                                           target_replace_module=L.UNET_EXTENDED_TARGET_REPLACE, r=2)
+    want = [p for x in m.modules() if isinstance(x, (L.LoraInjectedLinear, L.LoraInjectedConv2d))
+            for p in (x.lora_up.weight, x.lora_down.weight)]
+    got = [p for x in fresh.modules() if isinstance(x, (L.LoraInjectedLinear, L.LoraInjectedConv2d))
+           for p in (x.lora_up.weight, x.lora_down.weight)]
+    assert len(got) == len(want) and all(torch.equal(a.half().float(), b.float()) or torch.equal(a.half(), b.half())
+                                         for a, b in zip(want, got))
+    from safetensors import safe_open
+    f = safe_open(str(tmp_path / "lora_weight.safetensors"), "pt", "cpu")
+    assert sum(k.endswith(":up") for k in f.keys()) == n_injected
+    # a caller-named target set that misses layers is refused instead of writing a partial checkpoint
+    tr.cfg.unet_targets = ("CrossAttention",)
+    with pytest.raises(ValueError, match="not under the target classes"):
+        tr.save_final()
