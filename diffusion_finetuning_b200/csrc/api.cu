@@ -68,6 +68,7 @@ cudaError_t launch_merge(const void*, void*, const void*, const void*, float, in
                          float*, cudaStream_t);
 cudaError_t launch_svd_epilogue(float*, const float*, float*, float, int, int, int, int,
                                 cudaStream_t);
+cudaError_t launch_absmean_any(const void*, const void*, float*, int, int, int, int, cudaStream_t);
 struct MergeItem { const void* Win; void* Wout; const void* up; const void* down; int N, K, r, tile0, tiles_k, pad; };
 long long merge_batch_plan(MergeItem*, int, int);
 cudaError_t launch_merge_batch(const MergeItem*, int, int, int, float, int, int, int, cudaStream_t);
@@ -766,7 +767,7 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   g_err[0] = 0;
   if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
-  if (r < 1 || r > 16) { set_error("lora_grads supports 1 <= r <= 16 (got %d)", r); return B200LORA_E_SHAPE; }
+  if (r < 1 || r > 64) { set_error("lora_grads supports 1 <= r <= 64 (got %d)", r); return B200LORA_E_SHAPE; }
   if (M <= 0) return 0;
   if (!dA && !dB) return 0;
   const int vec = 16 / dtype_size(io_dtype);
@@ -945,11 +946,11 @@ extern "C" int b200lora_absmean_accum(const void* up, const void* down, float* o
   g_err[0] = 0;
   if (!up || !down || !out_sum) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (!valid_dtype(lora_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
-  if (r < 1 || r > 16) { set_error("absmean supports 1 <= r <= 16"); return B200LORA_E_SHAPE; }
+  if (r < 1) { set_error("absmean needs r >= 1"); return B200LORA_E_SHAPE; }
   const int vec = 16 / dtype_size(lora_dtype);
-  if (K % vec) { set_error("absmean needs K %% %d == 0", vec); return B200LORA_E_ALIGN; }
   cudaError_t e;
-  if (lora_dtype == B200LORA_F32) e = launch_merge<float, float, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
+  if (r > 16 || (K % vec)) e = launch_absmean_any(up, down, out_sum, N, K, r, lora_dtype, stream);   // any rank / any K
+  else if (lora_dtype == B200LORA_F32) e = launch_merge<float, float, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
   else if (lora_dtype == B200LORA_F16) e = launch_merge<__half, __half, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
   else e = launch_merge<__nv_bfloat16, __nv_bfloat16, 1>(nullptr, nullptr, up, down, 0.f, N, K, r, out_sum, stream);
   if (e != cudaSuccess) { set_error("absmean launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }

@@ -315,7 +315,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         const bool nm = tile == sc.t0 || n_blk == 0;
         const bool lk = nm && tile + 1 < sc.t1 && n_blk + 1 != p.num_n_blk;
         if (lane == 0) TS2(2, it, 0);
-        mbar_wait(&accempty_bar[st], st_par ^ 1, S2_MMA_ACC_EMPTY);
+        mbar_wait_cluster(&accempty_bar[st], st_par ^ 1, S2_MMA_ACC_EMPTY);   // peer's TMEM reads: acquire.cluster
         tc_fence_after_sync();
         if (lane == 0) TS2(2, it, 1);
         if (nm && e > 0 && elect_one()) umma_commit_2sm(st_free_bar, 3);
@@ -328,13 +328,13 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         uint32_t par2 = st_par;
         if (st2 == NST) { st2 = 0; par2 ^= 1; }
         if (lk) {
-          mbar_wait(&accempty_bar[st2], par2 ^ 1, S2_MMA_ACC_EMPTY);
+          mbar_wait_cluster(&accempty_bar[st2], par2 ^ 1, S2_MMA_ACC_EMPTY);
           tc_fence_after_sync();
           main_loop(st2);
           if (lane == 0) TS2(2, it, 3);
         }
         if (nm) {
-          mbar_wait(tsm_full_bar, e & 1, S2_MMA_TSM);
+          mbar_wait_cluster(tsm_full_bar, e & 1, S2_MMA_TSM);     // peer's [sT | 1] st.shared: acquire.cluster
           tc_fence_after_sync();
           ++e;
         }
@@ -419,7 +419,11 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       }
       fence_proxy_async_smem();
       tc_fence_before_sync();
-      mbar_arrive_cluster(tsm0);
+      // the leader's tcgen05.mma reads THIS CTA's t_tile: the peer publishes with release.cluster (PTX memory
+      // model: a .cta-scope release does not order the st.shared above for an observer in another CTA); the
+      // leader's own T warps are in the observer's CTA, where the default .cta scope is the right one
+      if (leader) mbar_arrive(tsm_full_bar);
+      else mbar_arrive_cluster_release(tsm0);
       if (threadIdx.x == 128) TS2(3, it, 2);
       ++e;
     }
@@ -478,7 +482,10 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       // this warp's TMEM reads of the stage are complete: one arrival per warp on the leader
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&accempty_bar[st]), 0));
+      if (lane == 0) {     // peer: release.cluster (its TMEM reads are ordered before the leader's next MMA)
+        if (leader) mbar_arrive(&accempty_bar[st]);
+        else mbar_arrive_cluster_release(mapa_shared(smem_u32(&accempty_bar[st]), 0));
+      }
       if (lane == 0 && qd == 0) TS2(4 + half, it, 2);
     }
     if (lane == 0) tma_store_wait_all<0>();

@@ -160,6 +160,42 @@ template cudaError_t launch_merge<__nv_bfloat16, __nv_bfloat16, 1>(const void*, 
                                                                    const void*, float, int, int,
                                                                    int, float*, cudaStream_t);
 
+// ---- abs-sum for any rank / any K (inspect_lora on r > 16 layers; diagnostic, not bandwidth-tuned):
+// one output element per thread per step, the r-term dot product in fp32, rounded to the LoRA dtype like up @ down ----
+__global__ void absmean_any_kernel(const void* __restrict__ up, const void* __restrict__ down, int dt,
+                                   float* __restrict__ abs_sum, int N, int K, int r) {
+  float local = 0.f;
+  const long long total = (long long)N * K;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / K), k = (int)(i - (long long)n * K);
+    float p = 0.f;
+    for (int j = 0; j < r; ++j)
+      p = fmaf(load_as_float(up, dt, (long long)n * r + j), load_as_float(down, dt, (long long)j * K + k), p);
+    if (dt == B200LORA_F16) p = __half2float(__float2half_rn(p));
+    else if (dt == B200LORA_BF16) p = __bfloat162float(__float2bfloat16_rn(p));
+    local += fabsf(p);
+  }
+  __shared__ float ws[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += ws[w];
+    atomicAdd(abs_sum, s);
+  }
+}
+
+cudaError_t launch_absmean_any(const void* up, const void* down, float* out_sum, int N, int K, int r, int dt,
+                               cudaStream_t stream) {
+  long long total = (long long)N * K;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  absmean_any_kernel<<<blocks, 256, 0, stream>>>(up, down, dt, out_sum, N, K, r);
+  return cudaGetLastError();
+}
+
 // ---- SVD epilogue ----
 __global__ void svd_epilogue_kernel(float* __restrict__ U, const float* __restrict__ S,
                                     float* __restrict__ Vh, float hi, int do_scale, int N, int K,

@@ -320,13 +320,22 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
   return r;
 }
-// arrive on an mbarrier given by its shared::cluster address (the peer CTA's barrier).
-// Default .release.cta semantics on purpose: a cluster-scope release compiles to MEMBAR.ALL.GPU
-// (and a cluster-scope acquire wait to CCTL.IVALL) per call, which doubled the kernel time.  No
-// generic-proxy data crosses the pair here: what the peer publishes is smem for the tensor core
-// (fence.proxy.async before the arrive) and drained TMEM (tcgen05.wait::ld + fence before it).
+// arrive on an mbarrier given by its shared::cluster address (the peer CTA's barrier), default
+// .release.cta semantics.  ONLY for arrivals that publish nothing of their own: the per-k-block `full`
+// arrive of the peer's producer (the data of a stage is published by the TMA unit's complete_tx on the
+// same barrier, i.e. by the async proxy itself).  A cluster-scope release compiles to MEMBAR.ALL.GPU
+// (and a cluster-scope acquire wait to CCTL.IVALL) per call, which doubled the kernel time when it sat on
+// the per-k-block barriers.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
+}
+// the same with .release.cluster: for hand-offs where THIS thread's earlier work must be visible to the
+// other CTA of the pair — generic-proxy st.shared of the [sT | 1] tile (read by the leader's
+// tcgen05.mma.cta_group::2 from this CTA's shared memory) and tcgen05.ld reads of an accumulator stage
+// (overwritten by the leader's next MMA).  Once per row block / per tile, not per k-block; pairs with
+// mbar_wait_cluster (acquire.cluster) on the leader.
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;

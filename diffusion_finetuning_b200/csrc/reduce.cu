@@ -39,8 +39,8 @@ struct RedProblem {
 };
 
 template <typename T, int RP>
-__device__ __forceinline__ void load_p(const T* __restrict__ P, long long m, int r, float (&pv)[RP]) {
-  if (r == RP) {  // compact row of exactly RP elements: vector loads (row stride = RP*sizeof(T))
+__device__ __forceinline__ void load_p(const T* __restrict__ P, long long m, int r, int ldp, float (&pv)[RP]) {
+  if (r == RP && ldp == RP) {  // compact row of exactly RP elements: vector loads (row stride = RP*sizeof(T))
     constexpr int BYTES = RP * (int)sizeof(T);
     if constexpr (BYTES % 16 == 0) {
       const uint4* src = reinterpret_cast<const uint4*>(P + m * RP);
@@ -59,14 +59,14 @@ __device__ __forceinline__ void load_p(const T* __restrict__ P, long long m, int
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < RP; ++j) pv[j] = (j < r) ? to_f32(P[m * r + j]) : 0.f;
+    for (int j = 0; j < RP; ++j) pv[j] = (j < r) ? to_f32(P[m * ldp + j]) : 0.f;
   }
 }
 
 template <typename T, int RP>
 __global__ void __launch_bounds__(red::NT)
-lora_grad_reduce_kernel(const RedProblem p0, const RedProblem p1, int blocks0, int r, float scale,
-                        long long M) {
+lora_grad_reduce_kernel(const RedProblem p0, const RedProblem p1, int blocks0, int r, int ldp, float scale,
+                        long long M) {   // r ranks of P starting at the problem's P pointer, row stride ldp
   constexpr int VEC = 16 / sizeof(T);   // columns per lane
   constexpr int CT = 8 * VEC;           // columns per block
   __shared__ float red_s[8][CT][RP + 1];
@@ -104,7 +104,7 @@ lora_grad_reduce_kernel(const RedProblem p0, const RedProblem p1, int blocks0, i
       for (int u = 0; u < red::UNROLL; ++u)
         raw[u] = __ldg(reinterpret_cast<const uint4*>(Z + (m + 32 * u) * p.ldz + c0));
 #pragma unroll
-      for (int u = 0; u < red::UNROLL; ++u) load_p<T, RP>(P, m + 32 * u, r, pv[u]);
+      for (int u = 0; u < red::UNROLL; ++u) load_p<T, RP>(P, m + 32 * u, r, ldp, pv[u]);
 #pragma unroll
       for (int u = 0; u < red::UNROLL; ++u) {
         const T* zv = reinterpret_cast<const T*>(&raw[u]);
@@ -119,7 +119,7 @@ lora_grad_reduce_kernel(const RedProblem p0, const RedProblem p1, int blocks0, i
     for (; m < m_end; m += 32) {
       const uint4 raw = __ldg(reinterpret_cast<const uint4*>(Z + m * p.ldz + c0));
       float pv[RP];
-      load_p<T, RP>(P, m, r, pv);
+      load_p<T, RP>(P, m, r, ldp, pv);
       const T* zv = reinterpret_cast<const T*>(&raw);
 #pragma unroll
       for (int v = 0; v < VEC; ++v) {
@@ -455,7 +455,12 @@ template <typename T>
 static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* tmX, const void* Tm,
                                    const void* dT, float scale, float* dA, float* dB, float* partA,
                                    float* partB, long long M, int K, int N, int r, int sms,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, int ldp = 0, int j0 = 0) {
+  // ranks [j0, j0 + r) of T / dT whose rows hold ldp ranks (ldp = 0: compact, ldp = r); dA / dB point at the
+  // FULL gradients [ldp, K] / [N, ldp]
+  if (ldp == 0) ldp = r;
+  if (dB) dB += j0;
+  if (dA) dA += (long long)j0 * K;
   RedProblem pb = {}, pa = {};   // for the finalize kernel of the deterministic mode
   RedTcGroup grp = {};
   RedTcGeom g = {};
@@ -467,14 +472,14 @@ static cudaError_t launch_grads_tc(const CUtensorMap* tmDY, const CUtensorMap* t
   int nblk = 0;
   if (dB) {
     RedTcProb& q = grp.p[grp.n];
-    fill_tc_prob(q, Tm, r, 0, r, scale, dB, r, 1, partB, N);
+    fill_tc_prob(q, Tm, ldp, j0, r, scale, dB, ldp, 1, partB, N);
     q.block_start = nblk; nblk += q.col_blocks * splits;
     tms[grp.n++] = tmDY;
-    pb.out = dB; pb.out_cs = r; pb.out_js = 1; pb.partial = partB; pb.C = N; pb.splits = splits;
+    pb.out = dB; pb.out_cs = ldp; pb.out_js = 1; pb.partial = partB; pb.C = N; pb.splits = splits;
   }
   if (dA) {
     RedTcProb& q = grp.p[grp.n];
-    fill_tc_prob(q, dT, r, 0, r, scale, dA, 1, K, partA, K);
+    fill_tc_prob(q, dT, ldp, j0, r, scale, dA, 1, K, partA, K);
     q.block_start = nblk; nblk += q.col_blocks * splits;
     tms[grp.n++] = tmX;
     pa.out = dA; pa.out_cs = 1; pa.out_js = K; pa.partial = partA; pa.C = K; pa.splits = splits;
@@ -578,27 +583,44 @@ cudaError_t launch_lora_grads(const void* dY, const void* X, const void* Tm, con
                               float scale, float* dA, float* dB, float* partA, float* partB,
                               long long M, int K, int N, int r, const CUtensorMap* tmDY,
                               const CUtensorMap* tmX, int sms, cudaStream_t stream) {
-  if constexpr (sizeof(T) == 2) {
-    if (tmDY != nullptr && tmX != nullptr)
-      return launch_grads_tc<T>(tmDY, tmX, Tm, dT, scale, dA, dB, partA, partB, M, K, N, r, sms, stream);
-  }
-  RedProblem pb = {}, pa = {};
-  int nb = 0, na = 0;
-  if (dB) { fill_problem(pb, dY, N, Tm, dB, /*cs=*/r, /*js=*/1, partB, M, N, sizeof(T)); nb = pb.col_blocks * pb.splits; }
-  if (dA) { fill_problem(pa, X, K, dT, dA, /*cs=*/1, /*js=*/K, partA, M, K, sizeof(T)); na = pa.col_blocks * pa.splits; }
-  if (nb + na == 0) return cudaSuccess;
-  const int RPv = r <= 4 ? 4 : (r <= 8 ? 8 : 16);
+  // Ranks above 16 (the reference accepts any r <= min(in, out); --lora_rank 32 / 64 are common) run as
+  // windows of 16 ranks: one launch per window over the same Z, each adding into its own rows of dA /
+  // columns of dB.  (The deterministic workspace is sized for 16 ranks and reused: the launches are
+  // stream-ordered.)
+  for (int j0 = 0; j0 < r; j0 += 16) {
+    const int rc = (r - j0) < 16 ? (r - j0) : 16;
+    if constexpr (sizeof(T) == 2) {
+      if (tmDY != nullptr && tmX != nullptr) {
+        cudaError_t e = launch_grads_tc<T>(tmDY, tmX, Tm, dT, scale, dA, dB, partA, partB, M, K, N, rc, sms, stream,
+                                           r, j0);
+        if (e != cudaSuccess) return e;
+        continue;
+      }
+    }
+    const T* Tw = Tm ? reinterpret_cast<const T*>(Tm) + j0 : nullptr;
+    const T* dTw = dT ? reinterpret_cast<const T*>(dT) + j0 : nullptr;
+    float* dBw = dB ? dB + j0 : nullptr;
+    float* dAw = dA ? dA + (long long)j0 * K : nullptr;
+    RedProblem pb = {}, pa = {};
+    int nb = 0, na = 0;
+    if (dB) { fill_problem(pb, dY, N, Tw, dBw, /*cs=*/r, /*js=*/1, partB, M, N, sizeof(T)); nb = pb.col_blocks * pb.splits; }
+    if (dA) { fill_problem(pa, X, K, dTw, dAw, /*cs=*/1, /*js=*/K, partA, M, K, sizeof(T)); na = pa.col_blocks * pa.splits; }
+    if (nb + na == 0) return cudaSuccess;
+    const int RPv = rc <= 4 ? 4 : (rc <= 8 ? 8 : 16);
 #define LAUNCH(RP_)                                                                              \
   do {                                                                                           \
-    lora_grad_reduce_kernel<T, RP_><<<nb + na, red::NT, 0, stream>>>(pb, pa, nb, r, scale, M);  \
+    lora_grad_reduce_kernel<T, RP_><<<nb + na, red::NT, 0, stream>>>(pb, pa, nb, rc, r, scale, M);  \
     if ((partA && dA) || (partB && dB)) {                                                        \
       const int n0 = dB ? N * RP_ : 0, n1 = dA ? K * RP_ : 0;                                     \
-      lora_grad_finalize_kernel<RP_><<<(n0 + n1 + 255) / 256, 256, 0, stream>>>(pb, pa, n0, r, scale); \
+      lora_grad_finalize_kernel<RP_><<<(n0 + n1 + 255) / 256, 256, 0, stream>>>(pb, pa, n0, rc, scale); \
     }                                                                                            \
   } while (0)
-  if (RPv == 4) LAUNCH(4); else if (RPv == 8) LAUNCH(8); else LAUNCH(16);
+    if (RPv == 4) LAUNCH(4); else if (RPv == 8) LAUNCH(8); else LAUNCH(16);
 #undef LAUNCH
-  return cudaGetLastError();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 template cudaError_t launch_lora_grads<float>(const void*, const void*, const void*, const void*,

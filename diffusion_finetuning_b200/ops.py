@@ -122,6 +122,10 @@ def _compute_dtype(x, w0):
     return x.dtype
 
 
+# Largest LoRA rank the forward / backward kernels take (csrc/linear_simt.cu keeps the rank slices in shared memory).
+# r <= 16 runs on the tcgen05 kernels, 17..64 on the CUDA-core kernels with the reductions in windows of 16 ranks.
+MAX_RANK = 64
+
 # Optional launch profiler (bench.py installs one): an object with begin(kind, M, K, N, r, esize)
 # and end(), called on either side of every hot-path launch on the launching stream.
 PROFILER = None
@@ -181,6 +185,10 @@ class _LoraLinearFn(torch.autograd.Function):
             raise RuntimeError(f"input feature size {x.shape[-1]} != in_features {K}")
         if A.dtype != B.dtype:
             raise RuntimeError("lora_down and lora_up must share a dtype")
+        if r > MAX_RANK:
+            raise nat.B200LoraError(
+                f"LoRA rank {r} is above the {MAX_RANK} the CUDA kernels support (1..16 on the tcgen05 path, 17..{MAX_RANK} "
+                "on the CUDA-core path); the module can still be built, saved, loaded and merged at any rank")
         lead = x.shape[:-1]
         x2 = x.reshape(-1, K)
         if x2.dtype != cdt:

@@ -206,7 +206,8 @@ int b200lora_conv2d_grad_a(const void* X_nhwc, const void* dT, float scale, floa
  * dA/dB are fp32 accumulators (e.g. slices of the flat gradient arena).  The kernel ADDS
  * into them (zero them first for a plain gradient).  Either of dA/dB may be NULL to skip.
  * deterministic=1 uses a two-stage reduction through `workspace` (bytes from
- * b200lora_lora_grads_workspace) instead of fp32 atomics.
+ * b200lora_lora_grads_workspace) instead of fp32 atomics.  1 <= r <= 64; ranks above 16 run as windows of
+ * 16 ranks (one launch each) over the same dY / X.
  */
 int b200lora_lora_grads(const void* dY, const void* X, const void* T, const void* dT,
                         float scale, float* dA, float* dB,

@@ -42,6 +42,33 @@ def rel_err(a, b):
     return (a - b).norm().item() / (denom if denom > 0 else 1.0)
 
 
+def max_abs_err(a, b):
+    """Largest element error, relative to the largest reference element: one wrong element (a TMA-clipped column,
+    a stale tile corner) shows up here while it vanishes in a Frobenius ratio over millions of elements."""
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    denom = b.abs().max().item()
+    return (a - b).abs().max().item() / (denom if denom > 0 else 1.0)
+
+
+def worst_row_err(a, b):
+    """max over rows of |a_i - b_i|_2 relative to the RMS row norm of the reference: a wrong last ragged row (or a
+    wrong row block) reads ~1 here, whatever the size of the tensor."""
+    a = a.detach().double().cpu().reshape(-1, a.shape[-1])
+    b = b.detach().double().cpu().reshape(-1, b.shape[-1])
+    rms = b.norm(dim=1).pow(2).mean().sqrt().item()
+    return (a - b).norm(dim=1).max().item() / (rms if rms > 0 else 1.0)
+
+
+def check_close(a, b, tol, what=""):
+    """The BASELINE bar (`tol` on the Frobenius ratio) plus the two outlier metrics: worst row within 4x and
+    largest element error within 4x of `tol` (a single element of a 16-bit result may sit a rounding step away
+    from the fp32 reference: half an ulp of the largest element is 2e-3 for bf16)."""
+    errs = {"rel": rel_err(a, b), "row": worst_row_err(a, b), "max": max_abs_err(a, b)}
+    assert errs["rel"] < tol and errs["row"] < 4 * tol and errs["max"] < 4 * tol, (what, tol, errs)
+    return errs
+
+
 @pytest.fixture(scope="session")
 def reference_lora():
     """The real reference module, when the build container has it mounted."""

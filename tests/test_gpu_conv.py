@@ -6,7 +6,7 @@ import pytest
 import torch
 
 import diffusion_finetuning_b200 as L
-from conftest import rel_err
+from conftest import max_abs_err, rel_err, worst_row_err
 from oracle import lora_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -20,6 +20,13 @@ CASES = [
     (3, 96, 72, 10, 14, 3, 1, 1, 1, 16, False, 0.5),       # ragged pixels / channels, r = 16
     (1, 128, 64, 12, 12, 3, 1, 2, 2, 8, True, 1.0),        # dilation 2
     (2, 32, 40, 9, 9, 3, 1, 1, 1, 1, True, 1.3),           # Cin < 64 (zero-padded channel block)
+    # BASELINE config 3: the wide resnet convs, r = 16 — many k-blocks per tap, Cin not a multiple of
+    # the 5-stage ring, Cout split over several n tiles, the 1x1 shortcut with 2560 input channels
+    (2, 1280, 1280, 8, 8, 3, 1, 1, 1, 16, True, 1.0),
+    (2, 2560, 1280, 16, 16, 3, 1, 1, 1, 16, True, 1.0),
+    (2, 1920, 640, 32, 32, 3, 1, 1, 1, 16, True, 0.7),
+    (1, 960, 320, 64, 64, 3, 1, 1, 1, 16, True, 1.0),
+    (2, 2560, 1280, 8, 8, 1, 1, 0, 1, 16, True, 1.0),      # conv_shortcut of the widest up block
 ]
 
 
@@ -63,6 +70,11 @@ def test_conv_forward_backward_match_oracle(case, dtype):
             "dA": rel_err(md.lora_down.weight.grad, A.grad), "dB": rel_err(md.lora_up.weight.grad, B.grad)}
     bad = {k_: v for k_, v in errs.items() if not v < 2e-2}
     assert not bad, f"{case} {dtype}: {bad} (all {errs})"
+    # outliers: one wrong output pixel / channel tile vanishes in the Frobenius ratio.  Rows = pixels over channels.
+    nhwc = lambda t: t.detach().float().cpu().permute(0, 2, 3, 1)
+    for name, a, b_ in (("y", nhwc(y), nhwc(y_ref)), ("dx", nhwc(xd.grad), nhwc(xr.grad))):
+        assert worst_row_err(a, b_) < 8e-2 and max_abs_err(a, b_) < 8e-2, (case, dtype, name, worst_row_err(a, b_),
+                                                                            max_abs_err(a, b_))
 
 
 def test_conv_under_autocast_with_fp32_masters_and_channels_last():

@@ -56,3 +56,40 @@ def test_scale_and_swapped_weights_follow_at_call_time():
             att.to_k.lora_up.weight = new_up
             for m in (att.to_q, att.to_k, att.to_v):
                 assert rel_err(m(x), _oracle(m, x)) < 2e-2, fused
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("r", [32, 64, 20])
+def test_ranks_above_16_train(r, dtype, tol):
+    """The reference accepts any r <= min(in, out) (lora.py:36-39); `--lora_rank 32 / 64` are common.  Ranks above the
+    16 the tcgen05 kernels carry run on the CUDA-core kernels, the token reductions in windows of 16 ranks (atomic and
+    deterministic modes), `inspect_lora` on the any-rank abs-mean kernel."""
+    from diffusion_finetuning_b200 import ops
+    torch.manual_seed(r)
+    m = L.LoraInjectedLinear(192, 136, bias=True, r=r).to(DEV).to(dtype)
+    m.linear.requires_grad_(False)
+    with torch.no_grad():
+        m.lora_up.weight.normal_(0, 0.02)
+    m.scale = 0.6
+    x = torch.randn(3, 211, 192, device=DEV, dtype=dtype, requires_grad=True)
+    dy = torch.randn(3, 211, 136, device=DEV, dtype=dtype)
+    c = lambda t: t.detach().float().cpu()
+    want_y = _oracle(m, x)
+    dx, dA, dB = O.lora_linear_grads(c(x), c(m.linear.weight), None, c(m.lora_down.weight), c(m.lora_up.weight), 0.6, c(dy))
+    for det in (False, True):
+        m.zero_grad()
+        x.grad = None
+        y = ops.lora_linear(x, m.linear.weight, m.linear.bias, m.lora_down.weight, m.lora_up.weight, m.scale,
+                            deterministic=det)
+        y.backward(dy)
+        assert rel_err(y, want_y) < tol and rel_err(x.grad, dx) < tol
+        assert rel_err(m.lora_down.weight.grad, dA) < tol and rel_err(m.lora_up.weight.grad, dB) < tol, (
+            det, rel_err(m.lora_down.weight.grad, dA), rel_err(m.lora_up.weight.grad, dB))
+    moved = L.inspect_lora(torch.nn.Sequential(m))
+    assert abs(moved["0"][0] - O.lora_abs_mean(c(m.lora_up.weight), c(m.lora_down.weight))) < (1e-6 if dtype == torch.float32 else 1e-4)
+
+
+def test_rank_above_the_kernel_limit_fails_loudly_at_forward():
+    m = L.LoraInjectedLinear(256, 256, r=96).to(DEV)          # constructing, saving, merging stay possible
+    with pytest.raises(Exception, match="rank 96"):
+        m(torch.randn(2, 256, device=DEV))

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 import diffusion_finetuning_b200 as L
-from conftest import rel_err
+from conftest import check_close, rel_err
 from diffusion_finetuning_b200.unet_sd15 import CrossAttention
 from oracle import lora_oracle as O
 
@@ -61,11 +61,15 @@ def test_fused_attention_block_matches_oracle_and_unfused(cross, r):
         torch.nn.functional.mse_loss(y.float(), tgt.to(dev)).backward()
         return y, xx.grad, (None if cc is None else cc.grad)
 
-    y_ref, dx_ref, dc_ref = run(ref, "cpu", True)
+    # The oracle runs the whole block in FP32 on the CPU (the reference's fp32 path).  Between the LoRA layers sit
+    # stock bf16 kernels (SDPA, softmax) on the GPU side, so this block-level comparison carries their rounding too;
+    # the 2e-2 bar on the LoRA layers alone, against fp32 math on identical (rounded) inputs, is
+    # test_fused_siblings_at_census_shapes_match_fp32_oracle below.
+    y_ref, dx_ref, dc_ref = run(ref, "cpu", False)
     y_f, dx_f, dc_f = run(ours, DEV, True)
     y_u, dx_u, dc_u = run(unf, DEV, True)
     assert groups[0].fused_calls == 1 and groups[0].enabled and groups[0].pending is None
-    tol = 3e-2
+    tol = 2e-2
     assert rel_err(y_f, y_ref.float()) < tol and rel_err(dx_f, dx_ref) < tol
     if cross:
         assert rel_err(dc_f, dc_ref) < tol and rel_err(dc_f, dc_u) < 2e-2
@@ -75,7 +79,73 @@ def test_fused_attention_block_matches_oracle_and_unfused(cross, r):
             gf, gu, gr = getattr(b, nm).weight.grad, getattr(c, nm).weight.grad, getattr(a, nm).weight.grad
             assert gf is not None and gf.dtype == torch.float32
             assert rel_err(gf, gu) < 2e-2, (nm, rel_err(gf, gu))
-            assert rel_err(gf, gr) < 5e-2, (nm, rel_err(gf, gr))
+            assert rel_err(gf, gr) < 2e-2, (nm, rel_err(gf, gr))
+
+
+class _Siblings(torch.nn.Module):
+    """to_q / to_k / to_v (or to_k / to_v) of one attention block, nothing else: the fused launch in isolation."""
+
+    def __init__(self, K, N, names):
+        super().__init__()
+        for nm in names:
+            setattr(self, nm, torch.nn.Linear(K, N, bias=False))
+
+
+# (M, K, N, member names): the fused launches of one bench step at BASELINE size (SURVEY 8 census)
+FUSED_CENSUS = [
+    (32768, 320, 320, ("to_q", "to_k", "to_v")),
+    (8192, 640, 640, ("to_q", "to_k", "to_v")),
+    (2048, 1280, 1280, ("to_q", "to_k", "to_v")),
+    (512, 1280, 1280, ("to_q", "to_k", "to_v")),
+    (616, 768, 320, ("to_k", "to_v")),
+    (616, 768, 640, ("to_k", "to_v")),
+    (616, 768, 1280, ("to_k", "to_v")),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("case", FUSED_CENSUS)
+def test_fused_siblings_at_census_shapes_match_fp32_oracle(case, dtype):
+    """ONE fused forward launch, ONE K-segmented dX launch and ONE multi-problem reduction launch at full size against
+    fp32 CPU math (lora.py:49-50 and its autograd) on the same inputs rounded to the io dtype: 2e-2 (BASELINE), plus
+    the worst-row / max-element metrics.  Different scale per member, separate output gradients per member."""
+    M, K, N, names = case
+    r = 4
+    torch.manual_seed(M + N)
+    blk = type("CrossAttention", (_Siblings,), {})(K, N, names)      # the reference matches targets by class NAME
+    blk.requires_grad_(False)
+    L.inject_trainable_lora(blk, {"CrossAttention"}, r=r)
+    layers = [getattr(blk, nm) for nm in names]
+    g = torch.Generator().manual_seed(7)
+    rnd = lambda t: t.to(dtype).float()
+    with torch.no_grad():
+        for i, m in enumerate(layers):
+            m.linear.weight.copy_(rnd(m.linear.weight))
+            m.lora_up.weight.copy_(rnd(torch.randn(N, r, generator=g) * 0.02))
+            m.lora_down.weight.copy_(rnd(m.lora_down.weight))
+            m.scale = (1.0, 0.7, 0.35)[i]
+    x = rnd(torch.randn(M, K, generator=g))
+    dys = [rnd(torch.randn(M, N, generator=g)) for _ in names]
+    want = []
+    for m, dy in zip(layers, dys):
+        W0, A, B = m.linear.weight.detach(), m.lora_down.weight.detach(), m.lora_up.weight.detach()
+        y = O.lora_linear_forward(x, W0, None, A, B, m.scale)
+        dx, dA, dB = O.lora_linear_grads(x, W0, None, A, B, m.scale, dy)
+        want.append((y, dx, dA, dB))
+    blk.to(DEV)
+    groups = L.fuse_sibling_projections(blk)
+    assert len(groups) == 1 and len(groups[0].layers) == len(names)
+    xd = x.to(DEV).requires_grad_(True)
+    with torch.autocast("cuda", dtype=dtype):
+        ys = [m(xd) for m in layers]
+    assert groups[0].fused_calls == 1
+    loss = sum((y.float() * dy.to(DEV)).sum() for y, dy in zip(ys, dys))
+    loss.backward()
+    for i, (m, (y, dx, dA, dB)) in enumerate(zip(layers, want)):
+        check_close(ys[i], y, 2e-2, f"y[{names[i]}]")
+        check_close(m.lora_down.weight.grad, dA, 2e-2, f"dA[{names[i]}]")
+        check_close(m.lora_up.weight.grad, dB, 2e-2, f"dB[{names[i]}]")
+    check_close(xd.grad, sum(w[1] for w in want), 2e-2, "dx (sum over members)")
 
 
 def test_group_switches_itself_off_when_inputs_differ_and_fp32_is_left_alone():
