@@ -317,6 +317,11 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
     p.cv_dil_h = cg->dil_h; p.cv_dil_w = cg->dil_w;
   }
   p.M = M; p.Kc = Kc; p.Nout = Nout; p.r = r;
+  {   // B200LORA_WPREFETCH=0 switches the pre-wait W loads off (A/B measurements)
+    static int wp = -1;
+    if (wp < 0) { const char* e = getenv("B200LORA_WPREFETCH"); wp = (e && e[0] == '0') ? 0 : 1; }
+    p.w_prefetch = wp;
+  }
   p.BN = tc_pick_bn(M, Kc, Nout, 256, dev_info().sms / 2);
   p.num_m_blk = (int)((M + 255) / 256);
   p.num_n_blk = (Nout + p.BN - 1) / p.BN;

@@ -159,7 +159,29 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   cluster_sync_all();       // peer barriers initialised before any remote arrive / multicast commit
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
-  pdl_wait();               // nothing above reads or writes global memory of earlier kernels
+  // W producer: the base-weight half-tiles of the first tile's first stages are requested BEFORE
+  // griddepcontrol.wait.  W is the frozen weight (or its cached cast / transpose / conv repack): no kernel that can
+  // still be running under programmatic launch writes it (only pack / GEMM / reduction kernels trigger early, and
+  // they write packs, activations and gradients), so these loads overlap the tail of the previous kernel and the
+  // first MMA finds its B operand already in shared memory.  X, the rank rows and the tail blocks come from earlier
+  // kernels and stay behind the wait; the stage's expect_tx is posted by the X producer as before (a transaction
+  // count may go negative until it is).
+  int w_pre = 0;
+  if (warp == 3 && p.w_prefetch && sc.t0 < sc.t1) {
+    w_pre = p.num_k_blk < stages ? p.num_k_blk : stages;
+    const uint64_t pol_w0 = policy_evict_last();
+    const uint32_t full0_b = mapa_shared(smem_u32(&full_bar[0]), 0);
+    const int n0 = (sc.t0 % p.num_n_blk) * BN;
+    if (elect_one()) {
+      for (int kb = 0; kb < w_pre; ++kb) {
+        uint8_t* b_dst = stage_base + (size_t)kb * stg_bytes + A_TILE_BYTES;
+        if (leader) tma_load_2d_2sm(b_dst, &tmWh, full0_b + kb * 8, kb * BK, n0, pol_w0);
+        else tma_load_2d_2sm(b_dst, &tmWa, full0_b + kb * 8, kb * BK, n0 + H, pol_w0);
+      }
+    }
+    __syncwarp();
+  }
+  pdl_wait();               // nothing above reads or writes global memory WRITTEN BY earlier kernels
   if (threadIdx.x == 0) TS2(0, 0, 1);
 
   if (warp == 0 || warp == 3) {
@@ -179,7 +201,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       const uint32_t main_tx = 2u * (A_TILE_BYTES + H * 128);   // both CTAs' bytes of one stage
       const uint32_t tail_tx = 2u * (BN / 2) * 128;
       const uint32_t full0_base = mapa_shared(smem_u32(&full_bar[0]), 0);   // leader's full_bar[0]
-      auto load_main = [&](int n_blk, int m_blk) {
+      auto load_main = [&](int n_blk, int m_blk, int w_done) {     // w_done: k-blocks whose W part is in flight
         const int n0 = n_blk * BN;
         // convolution: first output pixel of this CTA's 128 rows -> (image, oh, ow)
         int cv_n = 0, cv_h = 0, cv_w = 0;
@@ -213,9 +235,9 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                 tma_load_2d_2sm(a_dst, xm, full0, sk * BK, m_blk * 256 + (int)rank * BM, pol_x);
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
-              tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);                  // H rows
+              if (kb >= w_done) tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);   // H rows
             } else {
-              tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, n0 + H, pol_w);              // H-16 rows
+              if (kb >= w_done) tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, n0 + H, pol_w);   // H-16 rows
               tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
             }
           }
@@ -247,9 +269,9 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         int n1 = n_blk + 1, m1 = m_blk;
         if (n1 == p.num_n_blk) { n1 = 0; ++m1; }
         if (xrole && lane == 0) TS2(1, pit, 0);
-        load_main(n_blk, m_blk);
+        load_main(n_blk, m_blk, tile == sc.t0 ? w_pre : 0);
         if (xrole && lane == 0) TS2(1, pit, 1);
-        if (lk) load_main(n1, m1);
+        if (lk) load_main(n1, m1, 0);
         load_tail(n_blk);
         if (lk) load_tail(n1);
         if (xrole && lane == 0) TS2(1, pit, 2);
@@ -375,6 +397,31 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       uint32_t tv[16];
       tmem_ld_x16(tmem_base + lane_addr + st * ACC_STRIDE + BN, tv);
       tmem_ld_wait();
+      float tf[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        tf[j] = __uint_as_float(tv[j]) * p.scale;
+        if (p.has_bias && j == p.r) tf[j] = 1.0f;
+      }
+      if (e > 0) mbar_wait(st_free_bar, (e - 1) & 1, S2_T_FREE);
+      st_shared_v4(trow + ((0 ^ sw) << 4), pack2b<TIO>(tf[0], tf[1]), pack2b<TIO>(tf[2], tf[3]),
+                   pack2b<TIO>(tf[4], tf[5]), pack2b<TIO>(tf[6], tf[7]));
+      st_shared_v4(trow + ((1 ^ sw) << 4), pack2b<TIO>(tf[8], tf[9]), pack2b<TIO>(tf[10], tf[11]),
+                   pack2b<TIO>(tf[12], tf[13]), pack2b<TIO>(tf[14], tf[15]));
+      if (p.tail_ksteps > 1) {
+        st_shared_v4(trow + ((2 ^ sw) << 4), pack2b<TIO>(1.0f, 0.f), 0u, 0u, 0u);
+        st_shared_v4(trow + ((3 ^ sw) << 4), 0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before_sync();
+      // the leader's tcgen05.mma reads THIS CTA's t_tile: the peer publishes with release.cluster (PTX memory
+      // model: a .cta-scope release does not order the st.shared above for an observer in another CTA); the
+      // leader's own T warps are in the observer's CTA, where the default .cta scope is the right one
+      if (leader) mbar_arrive(tsm_full_bar);
+      else mbar_arrive_cluster_release(tsm0);
+      // T_out (saved for the backward) goes to global memory AFTER the hand-off: the cluster-scope release above is
+      // a MEMBAR.GPU, which would otherwise sit on the MMA's critical path until these stores are acknowledged
+      // (measured +2.5 us per launch at 128 row blocks when the stores came first)
       if (t_out != nullptr && n_blk == 0 && gm < p.M) {
         TIO* dst = t_out + gm * p.r;
         if (p.r == 4) {
@@ -402,28 +449,6 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             if (j < p.r) dst[j] = TIO(__uint_as_float(tv[j]));
         }
       }
-      float tf[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        tf[j] = __uint_as_float(tv[j]) * p.scale;
-        if (p.has_bias && j == p.r) tf[j] = 1.0f;
-      }
-      if (e > 0) mbar_wait(st_free_bar, (e - 1) & 1, S2_T_FREE);
-      st_shared_v4(trow + ((0 ^ sw) << 4), pack2b<TIO>(tf[0], tf[1]), pack2b<TIO>(tf[2], tf[3]),
-                   pack2b<TIO>(tf[4], tf[5]), pack2b<TIO>(tf[6], tf[7]));
-      st_shared_v4(trow + ((1 ^ sw) << 4), pack2b<TIO>(tf[8], tf[9]), pack2b<TIO>(tf[10], tf[11]),
-                   pack2b<TIO>(tf[12], tf[13]), pack2b<TIO>(tf[14], tf[15]));
-      if (p.tail_ksteps > 1) {
-        st_shared_v4(trow + ((2 ^ sw) << 4), pack2b<TIO>(1.0f, 0.f), 0u, 0u, 0u);
-        st_shared_v4(trow + ((3 ^ sw) << 4), 0u, 0u, 0u, 0u);
-      }
-      fence_proxy_async_smem();
-      tc_fence_before_sync();
-      // the leader's tcgen05.mma reads THIS CTA's t_tile: the peer publishes with release.cluster (PTX memory
-      // model: a .cta-scope release does not order the st.shared above for an observer in another CTA); the
-      // leader's own T warps are in the observer's CTA, where the default .cta scope is the right one
-      if (leader) mbar_arrive(tsm_full_bar);
-      else mbar_arrive_cluster_release(tsm0);
       if (threadIdx.x == 128) TS2(3, it, 2);
       ++e;
     }

@@ -464,12 +464,15 @@ def lora_abs_mean(up, down):
         return acc.item() / float(N * K)
 
 
-def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99):
+def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99, driver=None):
     """Rank-r factorisation of one weight difference (reference cli_svd.py:69-84).
 
-    The SVD stays on cuSOLVER (torch.linalg.svd driver gesvd, economy size: only the top-r
-    triplets are kept, so `full_matrices` of the reference is wasted work); U·diag(S), the symmetric clamp at the
-    `clamp_quantile` quantile of [U, Vh] and the slicing run in the epilogue kernel.
+    The SVD stays on cuSOLVER through `torch.linalg.svd`, economy size (`full_matrices=False`: only the top-r
+    triplets are kept, the reference's full `U [N, N]` — 419 MB at N = 10240 — is wasted work).  `driver=None` is
+    torch's default for CUDA tensors, i.e. exactly the call the reference makes on `device="cuda:0"`
+    (cli_svd.py:69: Jacobi `gesvdj`, QR `gesvd` if it does not converge); `driver="gesvd"` forces the QR driver, whose
+    fp32 factors sit closer to LAPACK's (1e-6 vs 5e-5 in the rank-4 product) at twice the time.  U·diag(S), the
+    symmetric clamp at the `clamp_quantile` quantile of [U, Vh] and the slicing run in the epilogue kernel.
     Returns (U [N,r], Vh [r,K]) fp32 — the `[up, down]` pair the reference saves.
     `clamp_quantile=None` skips the clamp (not a reference mode; used to test the factorisation,
     because the clamp threshold depends on the SVD's arbitrary sign convention).
@@ -478,9 +481,7 @@ def svd_distill_matrix(delta, rank=4, clamp_quantile=0.99):
     dev = delta.device if delta.is_cuda else _cuda_device()
     with torch.no_grad():
         mat = delta.detach().to(dev).float()
-        # driver="gesvd": cuSOLVER's QR-iteration SVD.  torch's default on CUDA is the Jacobi
-        # driver (gesvdj), whose fp32 factors were measured 7e-3 off the LAPACK result on B200.
-        U, S, Vh = torch.linalg.svd(mat, full_matrices=False, driver="gesvd")
+        U, S, Vh = torch.linalg.svd(mat, full_matrices=False, driver=driver)
         U = U[:, :rank].contiguous()
         S = S[:rank].contiguous()
         Vh = Vh[:rank, :].contiguous()
