@@ -199,16 +199,54 @@ class _LoraConv2dFn(torch.autograd.Function):
         return dx, None, None, dA, dB, None, None, None
 
 
+def _outside_kernel(module, x, cdt):
+    """Why this call cannot take the tcgen05 implicit-GEMM kernel, or None.  The kernel covers what the SD-1.5 resnets
+    use (16-bit io, groups 1, zero padding, r <= 16, channel counts that are multiples of 8, stride 1 when training)."""
+    conv = module.conv
+    if cdt not in (torch.bfloat16, torch.float16):
+        return "fp32 io (the implicit-GEMM kernel is 16-bit)"
+    if conv.groups != 1:
+        return "groups != 1"
+    if isinstance(conv.padding, str) or conv.padding_mode != "zeros":
+        return "non-zero padding mode"
+    if module.training and module.dropout.p > 0.0:
+        return "active dropout on the LoRA branch"
+    if module.r > 16:
+        return "rank above 16"
+    if conv.in_channels % 8 or conv.out_channels % 8:
+        return "channel counts not multiples of 8"
+    if torch.is_grad_enabled() and _pair(conv.stride) != (1, 1) and (
+            x.requires_grad or module.lora_down.weight.requires_grad or module.lora_up.weight.requires_grad):
+        return "strided convolution in training"
+    return None
+
+
+def _library_path(module, x, cdt):
+    """Upstream `LoraInjectedConv2d.forward` evaluated by cuDNN (three library convolutions, autograd backward) for the
+    geometries listed in `_outside_kernel`: the layer stays a drop-in for any nn.Conv2d the injector can meet, on the
+    GPU, in the call's own precision.  NOT a CPU / no-extension fallback: CUDA tensors only, and the extension must load."""
+    nat.require_cuda(x, "LoraInjectedConv2d.forward")
+    nat.lib()
+    conv = module.conv
+    A, B = module.lora_down.weight, module.lora_up.weight
+    if not isinstance(module.selector, nn.Identity):
+        sel = module.selector.weight.reshape(module.r, module.r).to(A.dtype)
+        A = torch.einsum("ij,jckl->ickl", sel, A)
+    base = conv(x)                                        # honours padding_mode / groups / stride / autocast
+    t = conv._conv_forward(x, A, None)                    # lora_down: the base conv's geometry (incl. padding mode)
+    up = torch.nn.functional.conv2d(t, B)                 # lora_up: 1x1
+    return base + module.dropout(up) * module.scale
+
+
 def lora_conv2d(module, x):
     """Forward of LoraInjectedConv2d (called by the module)."""
     conv = module.conv
-    if conv.groups != 1:
-        raise nat.B200LoraError("LoraInjectedConv2d: groups != 1 is not supported on the implicit-GEMM path")
-    if isinstance(conv.padding, str) or conv.padding_mode != "zeros":
-        raise nat.B200LoraError("LoraInjectedConv2d: only explicit zero padding is supported")
-    if module.training and module.dropout.p > 0.0:
-        raise nat.B200LoraError("LoraInjectedConv2d: dropout on the LoRA branch is not supported on the fused "
-                                "path (parity is defined at dropout = 0); set dropout_p = 0")
+    cdt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+    why = _outside_kernel(module, x, cdt)
+    if why is not None:
+        module._last_path = "cudnn: " + why
+        return _library_path(module, x, cdt)
+    module._last_path = "tcgen05 implicit GEMM"
     A = module.lora_down.weight
     if not isinstance(module.selector, nn.Identity):
         sel = module.selector.weight.reshape(module.r, module.r).to(A.dtype)     # diagonal r x r

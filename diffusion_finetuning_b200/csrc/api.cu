@@ -321,6 +321,18 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
     static int wp = -1;
     if (wp < 0) { const char* e = getenv("B200LORA_WPREFETCH"); wp = (e && e[0] == '0') ? 0 : 1; }
     p.w_prefetch = wp;
+    // How the PEER CTA's two hand-offs (staged [sT | 1] tile, drained accumulator stage) reach the leader's barriers:
+    //   2 (default) relay: the peer's warps arrive on peer-LOCAL barriers (.cta scope, arrivers and observer in one
+    //               CTA); a relay warp forwards each phase as an async-proxy transaction (16-byte DSMEM bulk copy with
+    //               complete_tx on the leader's barrier) — no generic-proxy release crosses the pair, no GPU-scope
+    //               fence in the MMA's path;
+    //   1           direct remote arrive with release.cluster, acquire.cluster wait on the leader (MEMBAR.GPU +
+    //               CCTL.IVALL per hand-off: +2..6 us per launch, measured);
+    //   0           direct remote arrive with the default .cta scope (what round 1 shipped; CUTLASS's 2-SM pipelines
+    //               do the same, but the PTX memory model does not order the peer's writes for the leader).
+    static int cs = -1;
+    if (cs < 0) { const char* e = getenv("B200LORA_CLUSTER_SCOPE"); cs = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2; }
+    p.cluster_scope = cs;
   }
   p.BN = tc_pick_bn(M, Kc, Nout, 256, dev_info().sms / 2);
   p.num_m_blk = (int)((M + 255) / 256);

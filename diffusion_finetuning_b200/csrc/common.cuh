@@ -51,6 +51,7 @@ struct TcParams {
   int conv, cv_S, cv_cpb, cv_Ho, cv_Wo;
   int cv_pad_h, cv_pad_w, cv_str_h, cv_str_w, cv_dil_h, cv_dil_w;
   int kseg;                   // != 0: X is split along K into tensors of kseg k-blocks each (<= 3)
+  int cluster_scope;          // pair kernel: release.cluster / acquire.cluster on the cross-CTA hand-offs (default 1)
   int w_prefetch;             // pair kernel: request the first stages' W half-tiles before griddepcontrol.wait
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;

@@ -108,7 +108,12 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   uint64_t* tfull_bar = accempty_bar + MAX_ACC;   // [1] per CTA (multicast commit)
   uint64_t* tsm_full_bar = tfull_bar + 1;         // [1] leader's: 256 thread arrivals
   uint64_t* st_free_bar = tsm_full_bar + 1;       // [1] per CTA (multicast commit)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_free_bar + 1);
+  // relay mode (p.cluster_scope == 2): the peer's hand-off arrivals stay INSIDE the peer CTA (these two barriers),
+  // a relay warp forwards each completed phase to the leader as an async-proxy transaction (bulk_copy_to_peer)
+  uint64_t* accempty_loc = st_free_bar + 1;       // [MAX_ACC] peer's: 8 epilogue-warp arrivals
+  uint64_t* tsm_loc = accempty_loc + MAX_ACC;     // [1] peer's: 128 thread arrivals
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tsm_loc + 1);
+  uint8_t* relay_box = reinterpret_cast<uint8_t*>(bars) + 512;   // [MAX_ACC + 1][16 B] source (peer) / sink (leader)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -143,12 +148,16 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       mbar_init(&full_bar[s], 2);   // leader: arrive.expect_tx; peer: remote arrive
       mbar_init(&empty_bar[s], 1);  // tcgen05.commit (multicast)
     }
+    const bool relay = p.cluster_scope == 2;
     for (int a = 0; a < MAX_ACC; ++a) {
       mbar_init(&accfull_bar[a], 1);
-      mbar_init(&accempty_bar[a], 2 * NUM_EPI_WARPS);
+      // direct modes: 16 warp arrivals (8 per CTA); relay mode: 8 local warps + the MMA warp's arrive.expect_tx
+      mbar_init(&accempty_bar[a], relay ? NUM_EPI_WARPS + 1 : 2 * NUM_EPI_WARPS);
+      mbar_init(&accempty_loc[a], NUM_EPI_WARPS);
     }
     mbar_init(tfull_bar, 1);
-    mbar_init(tsm_full_bar, 256);
+    mbar_init(tsm_full_bar, relay ? 129 : 256);
+    mbar_init(tsm_loc, 128);
     mbar_init(st_free_bar, 1);
     fence_mbar_init();
   }
@@ -333,13 +342,29 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       int n_blk = sc.t0 % p.num_n_blk;          // tracked incrementally: no div/mod per tile
       int st = 0;                               // TMEM stage of tile `it` and its use parity
       uint32_t st_par = 0;
+      const bool relay = p.cluster_scope == 2;
+      const int nt = sc.t1 - sc.t0;
+      // relay mode: a phase of accempty / tsm_full completes on 8 (128) LOCAL arrivals + this warp's arrive.expect_tx
+      // + the 16 bytes the peer's relay warp sends when the peer's half of the hand-off is done.  The post for the
+      // phase that tile `i` on stage s will complete goes out when the tile takes the stage — and only if a later tile
+      // will wait for it (the relay sends under the same condition: nothing may be in flight towards a CTA that exits).
+      auto post_acc = [&](int s_, int i_) {
+        if (relay && i_ + NST < nt && elect_one()) mbar_arrive_expect_tx(&accempty_bar[s_], 16);
+        __syncwarp();
+      };
+      auto wait_acc = [&](int s_, uint32_t par_) {
+        if (p.cluster_scope == 1) mbar_wait_cluster(&accempty_bar[s_], par_, S2_MMA_ACC_EMPTY);   // acquire.cluster
+        else mbar_wait(&accempty_bar[s_], par_, S2_MMA_ACC_EMPTY);
+      };
       for (int tile = sc.t0; tile < sc.t1;) {
         const bool nm = tile == sc.t0 || n_blk == 0;
         const bool lk = nm && tile + 1 < sc.t1 && n_blk + 1 != p.num_n_blk;
         if (lane == 0) TS2(2, it, 0);
-        mbar_wait_cluster(&accempty_bar[st], st_par ^ 1, S2_MMA_ACC_EMPTY);   // peer's TMEM reads: acquire.cluster
+        wait_acc(st, st_par ^ 1);
         tc_fence_after_sync();
+        post_acc(st, it);
         if (lane == 0) TS2(2, it, 1);
+        if (nm && relay && elect_one()) mbar_arrive_expect_tx(tsm_full_bar, 16);    // this row block's T hand-off
         if (nm && e > 0 && elect_one()) umma_commit_2sm(st_free_bar, 3);
         __syncwarp();
         main_loop(st);
@@ -350,13 +375,15 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         uint32_t par2 = st_par;
         if (st2 == NST) { st2 = 0; par2 ^= 1; }
         if (lk) {
-          mbar_wait_cluster(&accempty_bar[st2], par2 ^ 1, S2_MMA_ACC_EMPTY);
+          wait_acc(st2, par2 ^ 1);
           tc_fence_after_sync();
+          post_acc(st2, it + 1);
           main_loop(st2);
           if (lane == 0) TS2(2, it, 3);
         }
         if (nm) {
-          mbar_wait_cluster(tsm_full_bar, e & 1, S2_MMA_TSM);     // peer's [sT | 1] st.shared: acquire.cluster
+          if (p.cluster_scope == 1) mbar_wait_cluster(tsm_full_bar, e & 1, S2_MMA_TSM);     // peer's [sT | 1] st.shared: acquire.cluster
+          else mbar_wait(tsm_full_bar, e & 1, S2_MMA_TSM);
           tc_fence_after_sync();
           ++e;
         }
@@ -372,6 +399,53 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         }
         it += adv;
         tile += adv;
+      }
+    }
+    else if (p.cluster_scope == 2) {
+      // =============================== relay (peer CTA only) ==========================
+      // The peer's T warps and epilogue warps arrive on PEER-LOCAL barriers (.cta scope: arrivers and observer share a
+      // CTA).  This warp observes each completed phase and forwards it to the leader as an async-proxy transaction on
+      // the leader's barrier — a 16-byte distributed-shared-memory bulk copy with complete_tx — so no generic-proxy
+      // release has to cross the CTA pair and no GPU-scope fence sits in the MMA's path.
+      const int nt = sc.t1 - sc.t0;
+      const int n_rb = nt > 0 ? 1 + ((sc.t1 - 1) / sc.nnb - sc.t0 / sc.nnb) : 0;
+      int ia = 0, sa = 0, et = 0;
+      uint32_t pa = 0;
+      const int na = nt > NST ? nt - NST : 0;      // accumulator releases a later tile waits for
+      const long long t0c = clock64();
+      // lane 0 observes (acquire) and forwards; the other lanes only follow its control flow
+      auto seen = [&](uint64_t* bar, uint32_t parity) {
+        int ok = 0;
+        if (lane == 0) ok = mbar_try_wait(bar, parity) ? 1 : 0;
+        return __shfl_sync(0xffffffffu, ok, 0) != 0;
+      };
+      while (ia < nt || et < n_rb) {
+        if (ia < nt && seen(&accempty_loc[sa], pa)) {
+          if (ia < na && lane == 0) {
+            tc_fence_after_sync();
+            tc_fence_before_sync();
+            bulk_copy_to_peer(mapa_shared(smem_u32(relay_box + 16 * sa), 0), relay_box + 16 * sa, 16,
+                              mapa_shared(smem_u32(&accempty_bar[sa]), 0));
+          }
+          __syncwarp();
+          ++ia;
+          if (++sa == NST) { sa = 0; pa ^= 1; }
+        }
+        if (et < n_rb && seen(tsm_loc, et & 1)) {
+          if (lane == 0) {
+            tc_fence_after_sync();
+            tc_fence_before_sync();
+            bulk_copy_to_peer(mapa_shared(smem_u32(relay_box + 16 * MAX_ACC), 0), relay_box + 16 * MAX_ACC, 16,
+                              mapa_shared(smem_u32(tsm_full_bar), 0));
+          }
+          __syncwarp();
+          ++et;
+        }
+        if (clock64() - t0c > B200LORA_WATCHDOG_CYCLES) {
+          atomicCAS(&g_watchdog_code, 0u, 0x80000000u | (30u << 16) | (blockIdx.x & 0xffffu));
+          __threadfence_system();
+          __trap();
+        }
       }
     }
   } else if (warp >= 4 && warp < 8) {
@@ -418,7 +492,9 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       // model: a .cta-scope release does not order the st.shared above for an observer in another CTA); the
       // leader's own T warps are in the observer's CTA, where the default .cta scope is the right one
       if (leader) mbar_arrive(tsm_full_bar);
-      else mbar_arrive_cluster_release(tsm0);
+      else if (p.cluster_scope == 2) mbar_arrive(tsm_loc);                 // relay mode: stays in this CTA
+      else if (p.cluster_scope == 1) mbar_arrive_cluster_release(tsm0);
+      else mbar_arrive_cluster(tsm0);
       // T_out (saved for the backward) goes to global memory AFTER the hand-off: the cluster-scope release above is
       // a MEMBAR.GPU, which would otherwise sit on the MMA's critical path until these stores are acknowledged
       // (measured +2.5 us per launch at 128 row blocks when the stores came first)
@@ -476,13 +552,29 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
       uint32_t v[2][32];
       auto live = [&](int c) { return c < n_units && n_blk * BN + c * EPI_COLS < p.Nout; };
       if (live(half)) tmem_ld_x32(acc_addr + half * EPI_COLS, v[0]);
+      bool released = false;
+      // this warp's TMEM reads of the stage are complete once the LAST chunk's tcgen05.wait::ld has returned: the
+      // arrival goes out right there, before that chunk is converted and stored, so the (cluster-scope) release
+      // overlaps the rest of the epilogue instead of extending the MMA's wait for the accumulator stage
+      auto release_stage = [&]() {
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) {     // peer: release.cluster (its TMEM reads are ordered before the leader's next MMA)
+          if (leader) mbar_arrive(&accempty_bar[st]);
+          else if (p.cluster_scope == 2) mbar_arrive(&accempty_loc[st]);   // relay mode: stays in this CTA
+          else if (p.cluster_scope == 1) mbar_arrive_cluster_release(mapa_shared(smem_u32(&accempty_bar[st]), 0));
+          else mbar_arrive_cluster(mapa_shared(smem_u32(&accempty_bar[st]), 0));
+        }
+        released = true;
+      };
 #pragma unroll
       for (int ci = 0; ci < MAX_CI; ++ci) {
         const int c = 2 * ci + half;
         if (live(c)) {
           tmem_ld_wait_dep(v[ci & 1]);
-          if (ci + 1 < MAX_CI && live(c + 2))
-            tmem_ld_x32(acc_addr + (c + 2) * EPI_COLS, v[(ci + 1) & 1]);
+          const bool more = ci + 1 < MAX_CI && live(c + 2);
+          if (more) tmem_ld_x32(acc_addr + (c + 2) * EPI_COLS, v[(ci + 1) & 1]);
+          else release_stage();
           if (lane == 0) tma_store_wait_read<1>();
           __syncwarp();
           const uint32_t dst = stg_row + buf * (32 * EPI_COLS * 2);
@@ -504,13 +596,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           buf ^= 1;
         }
       }
-      // this warp's TMEM reads of the stage are complete: one arrival per warp on the leader
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane == 0) {     // peer: release.cluster (its TMEM reads are ordered before the leader's next MMA)
-        if (leader) mbar_arrive(&accempty_bar[st]);
-        else mbar_arrive_cluster_release(mapa_shared(smem_u32(&accempty_bar[st]), 0));
-      }
+      if (!released) release_stage();      // a warp with no live chunk in this tile (ragged N) still owes its arrival
       if (lane == 0 && qd == 0) TS2(4 + half, it, 2);
     }
     if (lane == 0) tma_store_wait_all<0>();

@@ -2,13 +2,15 @@
 // (lora.py:410-424 `weight_apply_lora` loops over the layers; cli_lora_add.py:72-110 does it for a UNet's 144 and a
 // text encoder's 48 matrices).  One launch per matrix was launch-bound (144 x 7.6 us against 0.24 ms of HBM time for the
 // whole fp32 UNet); here a device-side table describes every matrix and a persistent grid walks a flat list of
-// [64 rows x 512 bytes] tiles across all of them, so the kernel is one long HBM stream.
+// [32 rows x 512 bytes] tiles across all of them, so the kernel is one long HBM stream.
 //
 // Rounding follows the reference expression exactly (same as merge.cu): the rank-r product is accumulated in fp32 and
 // rounded ONCE to the LoRA dtype (what `up @ down` yields), cast to the weight dtype, multiplied by alpha in fp32 and
 // rounded to the weight dtype, added in fp32 and rounded to the weight dtype.  All 16-bit roundings are PACKED
 // conversions of two values (F2FP on the ALU pipe): the scalar cvt.rn.f16.f32 form issues on the quarter-rate
 // conversion pipe and capped the 16-bit merge at ~2.4 TB/s.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -26,10 +28,11 @@ struct MergeItem {          // device-side record, 48 bytes
 
 namespace mb {
 constexpr int TX = 32;      // 16-byte vectors along K per tile (512 contiguous bytes per row)
-constexpr int TY = 8;       // row lanes
-constexpr int NT = TX * TY;
-constexpr int UNROLL = 4;   // rows in flight per thread
-constexpr int ROWS = 64;    // rows per tile (two batches of TY * UNROLL)
+constexpr int TY = 4;       // row lanes
+constexpr int NT = TX * TY; // 128 threads: FOUR CTAs per SM, so the fill / load / compute / store phases of a tile
+                            // (serial inside one CTA) overlap across four independent streams per SM
+constexpr int UNROLL = 4;   // rows in flight per thread (multi-pass path)
+constexpr int ROWS = 32;    // rows per tile: 8 per thread, all 8 loads in flight at once (single-pass path)
 }  // namespace mb
 
 // round two fp32 values to T (round-to-nearest-even) and widen them back
@@ -89,12 +92,45 @@ template <> struct WVec<__nv_bfloat16> : WVec16<__nv_bfloat16> {};
 
 template <typename TL> __device__ __forceinline__ float ld_l(const TL* p) { return to_f32(__ldg(p)); }
 
+// VEC consecutive LoRA elements as fp32: one 8 / 16 / 32-byte load when the address allows it
+template <typename TL, int VEC>
+__device__ __forceinline__ void ld_row(const TL* __restrict__ p, bool aligned, float (&out)[VEC]) {
+  constexpr int BYTES = VEC * (int)sizeof(TL);
+  if (aligned) {
+    if constexpr (BYTES == 8) {
+      const uint2 raw = __ldg(reinterpret_cast<const uint2*>(p));
+      const TL* e = reinterpret_cast<const TL*>(&raw);
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) out[v] = to_f32(e[v]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < BYTES / 16; ++i) {
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(p) + i);
+        const TL* e = reinterpret_cast<const TL*>(&raw);
+#pragma unroll
+        for (int v = 0; v < 16 / (int)sizeof(TL); ++v) out[i * (16 / (int)sizeof(TL)) + v] = to_f32(e[v]);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) out[v] = ld_l(p + v);
+  }
+}
+
 // JR: rank rows of `down` resident in registers per pass (r <= 4 -> 4, r <= 8 -> 8, larger r -> passes of 8)
+//
+// Per tile (r <= JR, the common case): the tile's rows of `up` (ROWS x r contiguous elements) go to shared memory with
+// one coalesced pass, the thread's r x VEC slice of `down` to registers with vector loads, then EIGHT independent
+// 16-byte loads of W per thread are in flight before the first is consumed (4 CTAs x 128 threads x 128 B = 64 KB per
+// SM: what HBM latency x bandwidth asks for; with 4 loads in flight the fp32 merge sat at 4.7 TB/s = 32 KB per SM).
 template <typename TW, typename TL, int JR>
-__global__ void __launch_bounds__(mb::NT, JR <= 4 ? 2 : 1)
+__global__ void __launch_bounds__(mb::NT, JR <= 4 ? 4 : 2)
 lora_merge_batch_kernel(const MergeItem* __restrict__ items, int n_items, int total_tiles, float alpha) {
   constexpr int VEC = WVec<TW>::VEC;
+  constexpr int RPT = mb::ROWS / mb::TY;            // rows per thread per tile (8)
+  __shared__ float s_up[2][mb::ROWS * JR];
   const int tx = threadIdx.x & (mb::TX - 1), ty = threadIdx.x / mb::TX;
+  int flip = 0;
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
     // which matrix: last item with tile0 <= tile (uniform across the block: broadcast loads)
     int lo = 0, hi = n_items - 1;
@@ -106,7 +142,6 @@ lora_merge_batch_kernel(const MergeItem* __restrict__ items, int n_items, int to
     const int local = tile - it.tile0;
     const int kc = local % it.tiles_k, panel = local / it.tiles_k;
     const int k0 = (kc * mb::TX + tx) * VEC;
-    if (k0 >= it.K) continue;                       // K % VEC == 0 (host-checked): whole vectors only
     const int n_begin = panel * mb::ROWS;
     const int n_end = min(n_begin + mb::ROWS, it.N);
     const TW* Win = static_cast<const TW*>(it.Win);
@@ -115,43 +150,49 @@ lora_merge_batch_kernel(const MergeItem* __restrict__ items, int n_items, int to
     const TL* down = static_cast<const TL*>(it.down);
     const int r = it.r, K = it.K;
     if (r <= JR) {
-      // ---- the whole rank fits one pass: the r x VEC slice of `down` stays in registers for the tile ----
-      float d[JR][VEC];
+      // ---- the tile's rows of `up`: (n_end - n_begin) * r contiguous elements -> shared memory, as fp32 ----
+      float* su = s_up[flip];
+      flip ^= 1;
+      const int cnt = (n_end - n_begin) * r;
+      for (int i = threadIdx.x; i < cnt; i += mb::NT) su[i] = ld_l(up + (long long)n_begin * r + i);
+      __syncthreads();      // (two buffers: the next tile's fill cannot overtake this tile's readers)
+      if (k0 < K) {                                   // K % VEC == 0 (host-checked): whole vectors only
+        float d[JR][VEC];
+        const bool d_al = ((reinterpret_cast<uintptr_t>(down) | ((uintptr_t)K * sizeof(TL))) & (VEC * sizeof(TL) - 1)) == 0;
 #pragma unroll
-      for (int j = 0; j < JR; ++j)
+        for (int j = 0; j < JR; ++j) {
+          if (j < r) ld_row<TL, VEC>(down + (long long)j * K + k0, d_al, d[j]);
+          else {
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) d[j][v] = (j < r) ? ld_l(down + (long long)j * K + k0 + v) : 0.f;
-      for (int nb = n_begin + ty; nb < n_end; nb += mb::TY * mb::UNROLL) {
-        uint4 raw[mb::UNROLL];
-        float u[mb::UNROLL][JR];
+            for (int v = 0; v < VEC; ++v) d[j][v] = 0.f;
+          }
+        }
+        uint4 raw[RPT];
 #pragma unroll
-        for (int q = 0; q < mb::UNROLL; ++q) {
-          const int n = nb + q * mb::TY;
+        for (int q = 0; q < RPT; ++q) {
+          const int n = n_begin + ty + q * mb::TY;
           if (n < n_end) raw[q] = __ldcs(reinterpret_cast<const uint4*>(Win + (long long)n * K + k0));
         }
 #pragma unroll
-        for (int q = 0; q < mb::UNROLL; ++q) {
-          const int n = nb + q * mb::TY;
-#pragma unroll
-          for (int j = 0; j < JR; ++j) u[q][j] = (n < n_end && j < r) ? ld_l(up + (long long)n * r + j) : 0.f;
-        }
-#pragma unroll
-        for (int q = 0; q < mb::UNROLL; ++q) {
-          const int n = nb + q * mb::TY;
+        for (int q = 0; q < RPT; ++q) {
+          const int ln = ty + q * mb::TY;
+          const int n = n_begin + ln;
           if (n >= n_end) continue;
           float p[VEC], w[VEC];
 #pragma unroll
           for (int v = 0; v < VEC; ++v) p[v] = 0.f;
 #pragma unroll
-          for (int j = 0; j < JR; ++j)
+          for (int j = 0; j < JR; ++j) {
+            const float u = (j < r) ? su[ln * r + j] : 0.f;
 #pragma unroll
-            for (int v = 0; v < VEC; ++v) p[v] = fmaf(u[q][j], d[j][v], p[v]);
+            for (int v = 0; v < VEC; ++v) p[v] = fmaf(u, d[j][v], p[v]);
+          }
           WVec<TW>::load(raw[q], w);
 #pragma unroll
           for (int v = 0; v < VEC; v += 2) {
             float a = p[v], b = p[v + 1];
             round2<TL>(a, b);                 // up @ down in the LoRA dtype
-            round2<TW>(a, b);                 // .type(weight.dtype)
+            if constexpr (!std::is_same<TL, TW>::value) round2<TW>(a, b);     // .type(weight.dtype)
             a = __fmul_rn(alpha, a); b = __fmul_rn(alpha, b);
             round2<TW>(a, b);                 // alpha * (...) is a tensor of the weight dtype
             w[v] = __fadd_rn(w[v], a); w[v + 1] = __fadd_rn(w[v + 1], b);
@@ -159,9 +200,9 @@ lora_merge_batch_kernel(const MergeItem* __restrict__ items, int n_items, int to
           __stcs(reinterpret_cast<uint4*>(Wout + (long long)n * K + k0), WVec<TW>::store(w));
         }
       }
-    } else {
+    } else if constexpr (JR == 8) {     // (the JR = 4 kernel is only launched when every rank is <= 4)
       // ---- r > JR (JR == 8 here): passes of 8 rank rows, product accumulated in registers per row ----
-      for (int nb = n_begin + ty; nb < n_end; nb += mb::TY * mb::UNROLL) {
+      for (int nb = n_begin + ty; nb < n_end && k0 < K; nb += mb::TY * mb::UNROLL) {
         uint4 raw[mb::UNROLL];
         float p[mb::UNROLL][VEC];
 #pragma unroll
@@ -227,7 +268,7 @@ long long merge_batch_plan(MergeItem* items, int n, int w_dtype) {
 template <typename TW, typename TL>
 static cudaError_t launch_merge_batch_t(const MergeItem* items_dev, int n, int total_tiles, int max_r, float alpha,
                                         int sms, cudaStream_t stream) {
-  int grid = sms * 8;
+  int grid = sms * 16;      // 4 resident CTAs per SM, 4 waves: short tails, tiles handed out round-robin
   if (grid > total_tiles) grid = total_tiles;
   if (grid < 1) grid = 1;
   if (max_r <= 4)

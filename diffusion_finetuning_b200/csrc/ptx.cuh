@@ -337,6 +337,17 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
 __device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
 }
+// 16-byte bulk copy from OWN shared memory into another CTA's shared memory (distributed shared memory), completion
+// signalled as complete_tx on THAT CTA's mbarrier: a cross-CTA arrival carried by the async proxy, like the TMA
+// loads and tcgen05.commit arrivals of the k-block pipeline (no generic-proxy release crosses the pair).
+__device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster_addr, const void* src_smem, uint32_t bytes,
+                                                  uint32_t bar_cluster_addr) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+          dst_cluster_addr),
+      "r"(smem_u32(src_smem)), "r"(bytes), "r"(bar_cluster_addr)
+      : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

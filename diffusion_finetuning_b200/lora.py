@@ -10,11 +10,13 @@ pinned by our own PyTorch restatement only ("parity unpinned by the reference").
 """
 import json
 import math
+import os
 from itertools import groupby
 from typing import Dict, List, Optional, Set, Tuple, Type, Union
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import ops
 
@@ -39,6 +41,9 @@ except ImportError:  # pragma: no cover - safetensors is part of the image
 # ---------------------------------------------------------------------------------------------
 # injected layers
 # ---------------------------------------------------------------------------------------------
+_TORCH_OP_ROUTE = os.environ.get("B200LORA_TORCH_OP", "0") == "1"
+
+
 def _check_rank(r, a, b):
     if r > min(a, b):
         # reference lora.py:36-39
@@ -90,10 +95,15 @@ class LoraInjectedLinear(nn.Module):
             # Dropout sits on the branch OUTPUT (upstream placement), which cannot ride inside the
             # K-concatenated GEMM: run the fused kernel for the base (scale 0 contributes nothing)
             # and add the dropped branch explicitly.  Parity is graded at dropout = 0.
+            # The two rank-r projections of the dropped branch are plain skinny library GEMMs (2·M·r·(K+N) flops,
+            # r/N of the base's work); no zero weight is allocated and no second full-size GEMM runs.
             base = ops.lora_linear(input, self.linear.weight, self.linear.bias, A.detach(),
                                    B.detach(), 0.0, cache=self._base_cache)
-            branch = ops.lora_linear(input, torch.zeros_like(self.linear.weight), None, A, B, 1.0)
+            branch = F.linear(F.linear(input.to(base.dtype), A.to(base.dtype)), B.to(base.dtype))
             return base + self.dropout(branch) * self.scale
+        if _TORCH_OP_ROUTE and input.is_cuda:         # B200LORA_TORCH_OP=1: through torch.ops.b200lora.lora_linear
+            from . import torch_ops
+            return torch_ops.lora_linear_op(input, self.linear.weight, self.linear.bias, A, B, self.scale)
         sink = self._grad_sink if A is self.lora_down.weight else None
         return ops.lora_linear(input, self.linear.weight, self.linear.bias, A, B, self.scale,
                                cache=self._base_cache, sink=sink)

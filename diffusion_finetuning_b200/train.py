@@ -616,9 +616,9 @@ def main(argv=None):
     from .fused import fuse_sibling_projections
     from .unet_sd15 import UNet2DConditionModel
     cfg = TrainConfig(**{f.name: getattr(a, f.name) for f in dataclasses.fields(TrainConfig)})
-    if a.extended and cfg.mixed_precision == "no":
-        raise SystemExit("--extended wraps the resnet convs in LoraInjectedConv2d, whose tensor-core path is 16-bit: "
-                         "run it with --mixed-precision bf16 (or fp16)")
+    if a.extended and cfg.mixed_precision == "no" and int(os.environ.get("RANK", "0")) == 0:
+        print("note: --extended in fp32: the resnet LoRA convs run on cuDNN (the implicit-GEMM kernel is 16-bit); "
+              "use --mixed-precision bf16 for the tensor-core path")
     torch.manual_seed(0)
     unet = (UNet2DConditionModel.tiny() if a.tiny else UNet2DConditionModel()).to(device)
     unet.requires_grad_(False)

@@ -92,10 +92,66 @@ def test_conv_under_autocast_with_fp32_masters_and_channels_last():
     assert rel_err(y, y_ref) < 2e-2
 
 
-def test_conv_fp32_without_autocast_fails_loudly():
-    m = L.LoraInjectedConv2d(64, 64, 3, 1, 1, r=4).to(DEV)
-    with pytest.raises(Exception, match="16-bit"):
+# geometries outside the implicit-GEMM kernel (which covers what the SD-1.5 resnets use): the layer answers through
+# cuDNN with upstream semantics instead of raising, so it is a drop-in for any nn.Conv2d the injector can meet
+# (N, Cin, Cout, H, k, stride, pad, groups, r, dtype, dropout, padding_mode)
+LIBRARY_CASES = [
+    (2, 64, 64, 12, 3, 1, 1, 1, 4, torch.float32, 0.0, "zeros"),       # fp32 io without autocast
+    (2, 64, 128, 12, 3, 2, 1, 1, 4, torch.bfloat16, 0.0, "zeros"),     # strided, training (downsampler-style)
+    (2, 64, 64, 12, 3, 1, 1, 4, 4, torch.bfloat16, 0.0, "zeros"),      # groups = 4
+    (2, 64, 64, 12, 3, 1, 1, 1, 32, torch.bfloat16, 0.0, "zeros"),     # rank above 16
+    (2, 60, 36, 12, 3, 1, 1, 1, 4, torch.bfloat16, 0.0, "zeros"),      # channels not multiples of 8
+    (2, 64, 64, 12, 3, 1, 1, 1, 4, torch.bfloat16, 0.0, "reflect"),    # padding mode
+]
+
+
+@pytest.mark.parametrize("case", LIBRARY_CASES)
+def test_geometries_outside_the_kernel_run_on_cudnn_with_upstream_semantics(case):
+    N, Cin, Cout, H, k, st, pad, groups, r, dtype, drop, pmode = case
+    torch.manual_seed(Cin + Cout + r)
+    src = torch.nn.Conv2d(Cin, Cout, k, st, pad, 1, groups, True, padding_mode=pmode)
+    m = L.LoraInjectedConv2d(Cin, Cout, k, st, pad, 1, groups, True, r=r)
+    m.conv = src
+    m.lora_down = torch.nn.Conv2d(Cin, r, k, st, pad, 1, groups, bias=False, padding_mode=pmode)
+    with torch.no_grad():
+        m.lora_down.weight.normal_(0, 0.1)
+        m.lora_up.weight.normal_(0, 0.05)
+    m.conv.requires_grad_(False)
+    m.scale = 0.6
+    x = torch.randn(N, Cin, H, H)
+    xr = x.to(dtype).float().clone().requires_grad_(True)
+    f = lambda t: t.detach().to(dtype).float()
+    if pmode == "zeros":
+        y_ref = O.lora_conv2d_forward(xr, f(src.weight), f(src.bias), f(m.lora_down.weight).requires_grad_(True),
+                                      f(m.lora_up.weight), 0.6, st, pad, 1, groups)
+    else:
+        xp = torch.nn.functional.pad(xr, (pad,) * 4, mode=pmode)
+        y_ref = O.lora_conv2d_forward(xp, f(src.weight), f(src.bias), f(m.lora_down.weight), f(m.lora_up.weight), 0.6,
+                                      st, 0, 1, groups)
+    y_ref.square().mean().backward()
+    md = m.to(DEV).to(dtype)
+    xd = x.to(DEV).to(dtype).requires_grad_(True)
+    y = md(xd)
+    assert md._last_path.startswith("cudnn"), md._last_path
+    y.float().square().mean().backward()
+    tol = 1e-3 if dtype == torch.float32 else 2e-2      # fp32: cuDNN convolutions run TF32 by default, as the reference's would
+    assert y.dtype == dtype and rel_err(y, y_ref) < tol and rel_err(xd.grad, xr.grad) < 2 * tol
+    assert md.lora_up.weight.grad is not None and md.lora_down.weight.grad.abs().sum() > 0
+
+
+def test_kernel_path_is_the_one_that_runs_for_resnet_geometry():
+    m = L.LoraInjectedConv2d(64, 64, 3, 1, 1, r=4).to(DEV).to(torch.bfloat16)
+    m(torch.randn(1, 64, 8, 8, device=DEV, dtype=torch.bfloat16))
+    assert m._last_path == "tcgen05 implicit GEMM"
+    m.float()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
         m(torch.randn(1, 64, 8, 8, device=DEV))
+    assert m._last_path == "tcgen05 implicit GEMM"
+    m.train()
+    m.dropout.p = 0.1
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        m(torch.randn(1, 64, 8, 8, device=DEV))
+    assert m._last_path.startswith("cudnn: active dropout")
 
 
 def test_extended_injection_runs_a_resnet_block():
