@@ -285,9 +285,15 @@ class StockTrainer:
         self.params = [p for m in self.layers for p in (m.lora_up.weight, m.lora_down.weight)]
         self.model = self.unet
         self.ddp = bool(ddp)
+        self._side = torch.cuda.Stream(device=device)
         if ddp:
+            # torch's recipe for whole-network capture of DDP: construct it (and warm it up) in a side-stream context,
+            # or the reducer's AccumulateGrad nodes are tied to the default stream and invalidate the capture
             from torch.nn.parallel import DistributedDataParallel as DDP
-            self.model = DDP(self.unet, device_ids=[device.index], broadcast_buffers=False)
+            self._side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(self._side):
+                self.model = DDP(self.unet, device_ids=[device.index], broadcast_buffers=False)
+            torch.cuda.current_stream(device).wait_stream(self._side)
         self.opt = torch.optim.AdamW(self.params, lr=1e-4, fused=True, capturable=capturable)
         self.device = device
         self.graph = None
@@ -307,7 +313,7 @@ class StockTrainer:
         """Whole-network capture as torch documents it: warm-up on a side stream (11 iterations for DDP: the
         reducer rebuilds its buckets and its logger synchronises during the first ones), then one capture."""
         self.static = {k: v.clone() for k, v in example.items()}
-        side = torch.cuda.Stream(device=self.device)
+        side = self._side
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):
             for _ in range(11 if self.ddp else 3):
@@ -873,9 +879,20 @@ def dp_replica_check(tr, device):
     hi, lo = flat.clone(), flat.clone()
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-    differing = int((hi != lo).sum().item())
-    return {"params_bit_identical_across_ranks": differing == 0, "differing_elements": differing,
-            "elements": flat.numel(), "checksum_i64": int(flat.to(torch.int64).sum().item())}
+    diff = hi != lo
+    differing = int(diff.sum().item())
+    out = {"params_bit_identical_across_ranks": differing == 0, "differing_elements": differing,
+           "elements": flat.numel(), "checksum_i64": int(flat.to(torch.int64).sum().item())}
+    if differing:          # which buckets of the gradient arena the diverged parameters belong to
+        per_bucket = [0] * len(tr.arena.buckets)
+        off = 0
+        for p in tr.arena.params:
+            n = p.numel()
+            per_bucket[tr.arena._slot[id(p)][2]] += int(diff[off:off + n].sum().item())
+            off += n
+        out["differing_per_bucket"] = per_bucket
+        out["bucket_sizes"] = [b.hi - b.lo for b in tr.arena.buckets]
+    return out
 
 
 def main():

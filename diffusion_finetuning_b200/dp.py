@@ -95,6 +95,7 @@ class LoraGradArena:
         self._sync = True
         self._comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
         self._comm_used = False
+        self._compute_stream = None
         for p, layer in entries:
             o, n, bi = self._slot[id(p)]
             view = self.flat[o:o + n].view_as(p)
@@ -131,10 +132,22 @@ class LoraGradArena:
             # the fp32 arena here)
             if param.dtype != torch.float32:
                 o, n, _ = self._slot[id(param)]
-                self.flat[o:o + n].add_(param.grad.reshape(-1).float())
-                param.grad.zero_()      # folded; finish() writes the reduced value back
+                with self._on_compute_stream():
+                    self.flat[o:o + n].add_(param.grad.reshape(-1).float())
+                    param.grad.zero_()      # folded; finish() writes the reduced value back
             self._ready(bi)
         return hook
+
+    def _on_compute_stream(self):
+        """The stream the step's kernels run on (taken in `zero()` on the caller's thread).  The hook itself runs on
+        the autograd thread under the stream its AccumulateGrad node was CREATED on — and that node outlives a step
+        whenever something keeps the step's loss alive (dp.GraphedStep keeps the captured one): in a later eager step
+        the hook would then see a stale side stream, the bucket's event would not cover the gradient kernels and the
+        all-reduce would race with them (found on 2 GPUs: replicas drifted apart bit by bit)."""
+        import contextlib
+        if self._compute_stream is None:
+            return contextlib.nullcontext()
+        return torch.cuda.stream(self._compute_stream)
 
     def _ready(self, bi):
         b = self.buckets[bi]
@@ -154,7 +167,7 @@ class LoraGradArena:
         if nccl:
             self._comm_used = True
             ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
+            ev.record(self._compute_stream or torch.cuda.current_stream(self.device))    # see _on_compute_stream
             with torch.cuda.stream(self._comm):
                 self._comm.wait_event(ev)
                 b.work = dist.all_reduce(view, op=op, group=self.group, async_op=True)
@@ -163,7 +176,9 @@ class LoraGradArena:
 
     # ------------------------------------------------------------------ public
     def zero(self):
-        """Zero the arena and re-arm the buckets (replaces optimizer.zero_grad())."""
+        """Zero the arena and re-arm the buckets (replaces optimizer.zero_grad()).  Call it on the stream the step
+        runs on: that stream is what the bucket events are recorded on."""
+        self._compute_stream = torch.cuda.current_stream(self.device) if self._comm is not None else None
         self.flat.zero_()
         for lp in self._lowp.values():
             lp.zero_()

@@ -55,6 +55,8 @@ def rel(a, b):
 def main():
     out_path = sys.argv[1]
     os.environ.setdefault("B200LORA_DETERMINISTIC", "1")     # reductions without atomics: run-to-run identical
+    torch.backends.cudnn.allow_tf32 = False                  # the stock convs between the LoRA layers in true fp32:
+    torch.backends.cuda.matmul.allow_tf32 = False            # a batch of 4 and two batches of 2 must agree to 1e-5
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)

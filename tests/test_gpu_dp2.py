@@ -22,6 +22,7 @@ def test_dp2_equals_single_process_on_concatenated_batch_nccl(tmp_path):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=540)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     res = json.load(open(out))
+    print(json.dumps(res))
     for name, row in res.items():
         assert row["eager_rel"] < row["tol"], (name, row)
         assert row["graph_rel"] < row["tol"], (name, row)
