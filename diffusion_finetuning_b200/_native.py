@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libb200lora.so")
 
 F32, F16, BF16 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+STATIC_SCRATCH_BYTES = 4 << 20      # B200LORA_STATIC_SCRATCH_BYTES (include/b200lora.h)
 W_NK, W_KN = 0, 1
 
 _DTYPE_CODE = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
@@ -44,6 +45,7 @@ SIGNATURES = {
     "b200lora_lora_grads": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32,
                                    _i32, _i32, _vp, _i64, _vp]),
     "b200lora_lora_grads_workspace": (_i64, [_i64, _i32, _i32, _i32]),
+    "b200lora_lora_grads_static": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_arena_adamw": (_i32, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _f32, _vp, _vp]),
     "b200lora_flat_axpby": (_i32, [_vp, _vp, _vp, _i64, _f32, _f32, _i32, _i32, _vp]),
     "b200lora_ti_grad_rows": (_i32, [_vp, _vp, _i64, _i32, _vp, _i32, _vp, _i32, _vp]),

@@ -136,13 +136,13 @@ static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
 // The tensor-map encoders are driver entry points and need the primary context CURRENT on the calling
 // thread; a thread whose first CUDA work is one of our calls (the autograd backward thread) has only
 // had cudaSetDevice, which binds lazily.  One runtime no-op per thread and device does the binding.
+static thread_local int g_bound_dev = -1;   // file scope: b200lora_lora_grads_static binds without cudaFree and records it here
 static void bind_context() {
-  static thread_local int bound_dev = -1;
   int dev = -1;
   cudaGetDevice(&dev);
-  if (dev != bound_dev) {
+  if (dev != g_bound_dev) {
     cudaFree(0);
-    bound_dev = dev;
+    g_bound_dev = dev;
   }
 }
 
@@ -826,6 +826,62 @@ extern "C" int b200lora_lora_grads(const void* dY, const void* X, const void* T,
 #undef RUN
   if (e != cudaSuccess) { set_error("lora_grads launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// No-allocation variant of the deterministic gradient reductions (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The [splits, C, rp] partial sums live in a file-scope device array that every GPU
+// loading this library holds until exit.  `g_static_scratch` is a host-side STAND-IN in host code, not a device
+// address: the pointer the kernels get comes from cudaGetSymbolAddress, once per thread and device, with that
+// device current (the call also binds the primary context to the thread, so the tensor-map encoders need no
+// cudaFree(0) on this path).  Every slot the finalize kernel reads is written by the same call's first stage
+// (reduce.cu: partial[(split * C + c) * rp + j] for every split, c < C, j < r), so nothing has to start at zero;
+// the array keeps the last call's contents and calls that overlap on the GPU (two streams, two threads) race.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[B200LORA_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_ptr(void** out) {
+  constexpr int MAX_DEV = 64;
+  static thread_local void* tl_ptr[MAX_DEV] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    set_error("lora_grads_static: no current device (%s)", cudaGetErrorString(e));
+    return B200LORA_E_CUDA;
+  }
+  if (!tl_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("lora_grads_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return B200LORA_E_CUDA;
+    }
+    tl_ptr[dev] = p;
+    g_bound_dev = dev;      // the runtime call above made the primary context current on this thread
+  }
+  *out = tl_ptr[dev];
+  return 0;
+}
+
+extern "C" int b200lora_lora_grads_static(const void* dY, const void* X, const void* T, const void* dT, float scale,
+                                          float* dA, float* dB, int64_t M, int K, int N, int r, int io_dtype,
+                                          b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  if (r < 1 || r > 64 || M < 0 || K < 1 || N < 1) { set_error("lora_grads_static: bad shape M=%lld K=%d N=%d r=%d", (long long)M, K, N, r); return B200LORA_E_SHAPE; }
+  const int64_t need = b200lora_lora_grads_workspace(M, K, N, r);
+  if (need > (int64_t)B200LORA_STATIC_SCRATCH_BYTES) {
+    set_error("lora_grads_static: M=%lld K=%d N=%d r=%d needs %lld bytes of scratch, above the built-in %lld "
+              "(use b200lora_lora_grads with a caller workspace)", (long long)M, K, N, r, (long long)need,
+              (long long)B200LORA_STATIC_SCRATCH_BYTES);
+    return B200LORA_E_SHAPE;
+  }
+  void* ws = nullptr;
+  int rc = static_scratch_ptr(&ws);
+  if (rc) return rc;
+  return b200lora_lora_grads(dY, X, T, dT, scale, dA, dB, M, K, N, r, io_dtype, /*deterministic=*/1, ws,
+                             (int64_t)B200LORA_STATIC_SCRATCH_BYTES, stream_);
 }
 
 extern "C" int b200lora_arena_adamw(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,

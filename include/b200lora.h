@@ -217,6 +217,26 @@ int b200lora_lora_grads(const void* dY, const void* X, const void* T, const void
 int64_t b200lora_lora_grads_workspace(int64_t M, int K, int N, int r);
 
 /*
+ * No-allocation variant of the deterministic reductions above.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arithmetic and launches as b200lora_lora_grads(...,
+ * deterministic = 1, workspace) — bit-identical results — but the two-stage partial sums live in a device array
+ * built into the library (B200LORA_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until exit)
+ * instead of a caller workspace.  The call itself issues no cudaMalloc / cudaFree and calls no allocating
+ * library routine; the caller still owns every input and output.
+ *   - shapes whose b200lora_lora_grads_workspace(M, K, N, r) exceeds B200LORA_STATIC_SCRATCH_BYTES are
+ *     rejected with B200LORA_E_SHAPE and a message naming both sizes (nothing is launched);
+ *   - all calls on a device share the one array, which keeps the previous call's contents (every slot a call
+ *     reads it has written first, so nothing needs clearing): calls that OVERLAP on the GPU — different
+ *     streams, different threads — race on it.  Serialise them on one stream.
+ */
+#define B200LORA_STATIC_SCRATCH_BYTES (4 << 20)
+int b200lora_lora_grads_static(const void* dY, const void* X, const void* T, const void* dT,
+                               float scale, float* dA, float* dB,
+                               int64_t M, int K, int N, int r, int io_dtype,
+                               b200lora_stream_t stream);
+
+/*
  * Fused sibling projections — layers that evaluate lora.py:49-50 on the SAME input (the to_q / to_k /
  * to_v of one attention block, all called on `hidden_states` by the caller of LoraInjectedLinear)
  * run as ONE problem over their concatenated outputs.
