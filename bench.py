@@ -800,9 +800,12 @@ def run_config5(args, device, rank):
             "config": {"workload": f"sd15_merge_144_unet_plus_48_clip_matrices_r{args.rank}_alpha_sweep_svd",
                        "l2": "inputs larger than L2: one merge pass reads and writes 1.77 GB (fp32) / 0.88 GB (16-bit)"},
             "gpu_launches": launches, "clocks": clk,
-            "roofline": {"kernel": "lora_merge_batch_kernel", "bound": "hbm", "achieved": merge["fp32"]["gbs"],
-                         "peak": pk["hbm"], "unit": "GB/s", "frac": merge["fp32"]["frac_hbm"], "traffic": None,
-                         "peak_source": pk["src"]},
+            "roofline": {"kernel": "lora_merge_stream_kernel (fp32 weights; bulk-copy ring, one launch for all 192 matrices)",
+                         "bound": "hbm", "achieved": merge["fp32"]["gbs"],
+                         "peak": pk["hbm"], "unit": "GB/s", "frac": merge["fp32"]["frac_hbm"], "traffic": _merge_traffic(),
+                         "peak_source": pk["src"],
+                         "fp16": {"achieved": merge["fp16"]["gbs"], "frac": merge["fp16"]["frac_hbm"]},
+                         "bf16": {"achieved": merge["bf16"]["gbs"], "frac": merge["bf16"]["frac_hbm"]}},
             "merge": merge, "scale_sweep": sweep, "svd_distill": svd}
     # ---- e2e: the public call on HOST-resident fp32 weights (cli_lora_add merges a CPU pipeline, cli_lora_add.py:74-78):
     # weights staged host -> device, one merge launch, results copied back, inside the timed region ----
@@ -825,6 +828,14 @@ def run_config5(args, device, rank):
         line["cpu_baseline"] = config5_cpu(args)
     _emit(line)
     return 0
+
+
+def _merge_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one fp32 whole-model merge launch, from the committed ncu capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("lora_merge_fp32_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
 
 
 def config5_cpu(args, seconds=20.0):

@@ -144,6 +144,49 @@ def test_merge_batch_one_launch_equals_oracle_and_per_matrix_kernel(wdt, ldt):
     assert [w.data_ptr() for w in dev_w] == ptrs and all(torch.equal(a, b) for a, b in zip(dev_w, got))
 
 
+@pytest.mark.parametrize("wdt,ldt", [(torch.float16, torch.float16), (torch.bfloat16, torch.bfloat16),
+                                     (torch.float16, torch.float32), (torch.float32, torch.float32),
+                                     (torch.float32, torch.float16), (torch.bfloat16, torch.float16)])
+@pytest.mark.parametrize("ranks", [(4, 4, 1, 3, 2, 4), (8, 5, 4, 8, 7, 6)])
+def test_merge_batch_streamed_kernel_bit_identical(wdt, ldt, ranks):
+    """The bulk-copy-ring merge kernel (every rank <= 8: `lora_merge_stream_kernel`, packed 16-bit arithmetic) against
+    the per-matrix kernel (fp32 arithmetic on unpacked values, merge.cu) BIT for bit, for the three forms alpha takes
+    in the kernel (1, representable in the weight dtype, neither), ragged tiles (N % 32, K % tile row), odd ranks
+    (scalar `up` reads) and `up` / `down` buffers that are not 16-byte aligned (read by the consumers from global
+    memory instead of the ring); and against the oracle's lora.py:423 expression on the CPU."""
+    g = torch.Generator().manual_seed(5)
+    dims = [(320, 320), (1280, 640), (77, 768), (65, 264), (33, 2056), (640, 2560)]
+    Ws = [(torch.randn(N, K, generator=g) * 0.03).to(wdt) for N, K in dims]
+    ups = [(torch.randn(N, r, generator=g) * 0.05).to(ldt) for (N, _), r in zip(dims, ranks)]
+    downs = [(torch.randn(r, K, generator=g) * 0.3).to(ldt) for (_, K), r in zip(dims, ranks)]
+    dW = [w.to(DEV) for w in Ws]
+
+    def shifted(t):          # same values, storage offset of one element: data_ptr not 16-byte aligned
+        buf = torch.empty(t.numel() + 1, dtype=t.dtype, device=DEV)
+        v = buf[1:].view(t.shape)
+        v.copy_(t)
+        assert v.is_contiguous() and v.data_ptr() % 16 != 0
+        return v
+
+    dU = [shifted(u) if i % 2 else u.to(DEV) for i, u in enumerate(ups)]
+    dD = [shifted(d) if i in (1, 2) else d.to(DEV) for i, d in enumerate(downs)]
+    for alpha in (1.0, 0.5, 0.6):
+        got = ops.merge_lora_weights(dW, dU, dD, alpha)
+        for w, u, d, y, hw, hu, hd in zip(dW, dU, dD, got, Ws, ups, downs):
+            single = ops.merge_lora_weight(w, u, d, alpha)
+            assert torch.equal(single, y), (alpha, tuple(w.shape), (single.float() - y.float()).abs().max().item())
+            want = O.merge_weight(hw, hu.to(hd.dtype), hd, alpha)
+            bad = (y.cpu() != want).float().mean().item()
+            # the CPU matmul of the reference may order its r-term fp32 sum differently: a last-place difference in a
+            # handful of elements is tolerated, a different rounding chain is not (it moves ~30 % of them)
+            assert bad < 2e-3, (alpha, tuple(w.shape), bad)
+    # in place over the same buffers
+    ptrs = [w.data_ptr() for w in dW]
+    want = ops.merge_lora_weights(dW, dU, dD, 0.6)
+    ops.merge_lora_weights(dW, dU, dD, 0.6, inplace=True)
+    assert [w.data_ptr() for w in dW] == ptrs and all(torch.equal(a, b) for a, b in zip(dW, want))
+
+
 def test_merge_batch_matches_reference_vectors():
     blob, meta = load_golden("merge_cases.safetensors")
     alpha = float(meta["alpha"])
@@ -299,9 +342,12 @@ def test_graphed_training_step_equals_eager(fused, monkeypatch):
     multi-problem reduction adds with fp32 atomics (order differs run to run): trajectory-level agreement."""
     import copy
     import itertools
+    from torch.nn.attention import SDPBackend
     from diffusion_finetuning_b200 import dp
     if not fused:
         monkeypatch.setenv("B200LORA_DETERMINISTIC", "1")
+        monkeypatch.setattr(torch.backends.cudnn, "deterministic", True)
+        monkeypatch.setattr(torch.backends.cudnn, "benchmark", False)
 
     def build():
         torch.manual_seed(0)
@@ -321,10 +367,15 @@ def test_graphed_training_step_equals_eager(fused, monkeypatch):
 
         def step(b):
             arena.zero()
-            with torch.autocast("cuda", dtype=torch.bfloat16):
-                pred = unet(b["latents"], b["t"], b["ctx"])
-            loss = torch.nn.functional.mse_loss(pred.float(), b["target"])
-            loss.backward()
+            # fused=False pins the STOCK kernels too (math SDPA, deterministic cuDNN algorithms): what is left between
+            # graph replay and eager is then only what our own launches do differently, i.e. nothing
+            with torch.nn.attention.sdpa_kernel(SDPBackend.MATH if not fused else
+                                                [SDPBackend.FLASH_ATTENTION, SDPBackend.EFFICIENT_ATTENTION,
+                                                 SDPBackend.CUDNN_ATTENTION, SDPBackend.MATH]):
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    pred = unet(b["latents"], b["t"], b["ctx"])
+                loss = torch.nn.functional.mse_loss(pred.float(), b["target"])
+                loss.backward()
             arena.finish()
             arena.clip_grad_norm_(1.0)
             opt.step()
@@ -347,13 +398,17 @@ def test_graphed_training_step_equals_eager(fused, monkeypatch):
         le = step_e(b).item()
         lg = graphed(b).item()
         assert abs(le - lg) <= (2e-2 if fused else 1e-3) * abs(le), (le, lg)
+    worst = 0.0
     for pe, pg in zip(ue.parameters(), ug.parameters()):
         if pe.requires_grad:
             if fused:   # Adam normalises: a gradient whose sign is atomic-order noise moves a weight by +-lr
                 assert rel_err(pg, pe) < 0.15
             else:       # measured up to 2e-4 across boxes: the STOCK kernels between the LoRA layers (cuDNN / SDPA
                 # backward) still accumulate with atomics; a stale pack or a missed launch shows up at 1e-2 and above
-                assert rel_err(pg, pe) <= 2e-3, rel_err(pg, pe)
+                worst = max(worst, rel_err(pg, pe))
+    print(f"graphed vs eager, fused={fused}: worst parameter rel_err after 5 steps {worst:.3e}")
+    if not fused:
+        assert worst <= 2e-3, worst
 
 
 @pytest.mark.parametrize("max_norm", [None, 0.05])
