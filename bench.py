@@ -400,6 +400,8 @@ class Trainer:
                 if isinstance(m, (L.LoraInjectedLinear, L.LoraInjectedConv2d)):
                     m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
         self.groups = L.fuse_sibling_projections(self.unet) if fuse else []
+        # GEGLU projections (only injected by the extended / default target sets: config 3): activation in the epilogue
+        self.geglu = L.fuse_geglu(self.unet) if fuse and os.environ.get("B200LORA_BENCH_GEGLU", "1") != "0" else []
         self.arena = dp.LoraGradArena(self.unet, bucket_bytes=1 << 20)
         self.arena.broadcast_params(0)
         if arena_optimizer:      # clip 1.0 + AdamW over the flat arenas: one C-ABI call per step
@@ -653,7 +655,7 @@ def config_dict(args, batch):
                        "AdamW lr 1e-4, clip 1.0" + (" (dp.ArenaAdamW)" if getattr(args, "arena_optimizer", False) else "")),
          "memory_format": getattr(args, "memory_format", "nchw"),
          "step_launch": "python" if getattr(args, "no_graph", False) else "whole step replayed as one CUDA graph",
-         "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch",
+         "sibling_fusion": "off" if getattr(args, "no_fuse", False) else "q/k/v and k/v LoRA layers of one attention block = one launch; GEGLU projections (config 3) with the activation in the GEMM epilogue",
          "l2": "inputs larger than L2: per-step activations (>10 GB) dwarf the 126 MB L2; no explicit flush"}
     return d
 

@@ -10,4 +10,4 @@ from .lora import (_find_children, _find_modules, _find_modules_old, _find_modul
 from . import ops  # noqa: F401
 
 __version__ = "0.1.0"
-from .fused import fuse_sibling_projections, unfuse_sibling_projections  # noqa: F401,E402
+from .fused import fuse_sibling_projections, unfuse_sibling_projections, fuse_geglu, unfuse_geglu  # noqa: F401,E402

@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200lora.so")
-SOURCES = ["api.cu", "linear_tc.cu", "linear_tc2.cu", "conv_aux.cu", "linear_simt.cu", "reduce.cu", "merge.cu", "merge_batch.cu", "optim.cu", "ti.cu", "flat.cu"]
+SOURCES = ["api.cu", "linear_tc.cu", "linear_tc2.cu", "conv_aux.cu", "linear_simt.cu", "reduce.cu", "merge.cu", "merge_batch.cu", "geglu.cu", "optim.cu", "ti.cu", "flat.cu"]
 HEADERS = ["common.cuh", "ptx.cuh", os.path.join("..", "..", "include", "b200lora.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [

@@ -33,7 +33,7 @@ int tc2_smem_bytes(int BN, int* stages_out);
 template <typename TIO>
 cudaError_t launch_tc2(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                        const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                       const TcParams&, int, cudaStream_t);
+                       const CUtensorMap&, const TcParams&, int, cudaStream_t);
 cudaError_t launch_conv_repack(const void*, int, void*, int, int, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_conv_pack(const void*, const void*, int, const void*, int, void*, void*, void*, int,
                              int, int, int, int, int, int, int, int, cudaStream_t);
@@ -74,6 +74,7 @@ long long merge_batch_plan(MergeItem*, int, int);
 cudaError_t launch_merge_batch(const MergeItem*, int, int, int, float, int, int, int, cudaStream_t);
 cudaError_t launch_arena_adamw(float*, float*, float*, float*, long long, float, float, float, float, float,
                                float, float*, cudaStream_t);
+cudaError_t launch_geglu_bwd(const void*, const void*, void*, long long, int, int, int, cudaStream_t);
 cudaError_t launch_flat_axpby(const void*, const void*, void*, long long, float, float, int, int, cudaStream_t);
 cudaError_t launch_ti_grad_rows(const void*, const long long*, long long, int, const long long*, int, float*, int,
                                 cudaStream_t);
@@ -303,14 +304,18 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
 struct ConvGeoH { int N, H, W, C, Ho, Wo, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w; };
 // X given as `n` tensors [M, cols] side by side along K (cols % 64 == 0, n <= 3)
 struct XSegs { int n; int cols; const void* ptr[3]; long long ld[3]; };
+// GEGLU projection (W = [hidden ; gate], Nout = 2*d_ff): also write hidden * gelu(gate) to out [M, d_ff]
+struct GegluH { int d_ff; void* out; long long ldo; int store_y; };
 
 static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, bool has_bias,
                    const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
                    void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
-                   cudaStream_t stream, const ConvGeoH* cg = nullptr, const XSegs* xs = nullptr) {
+                   cudaStream_t stream, const ConvGeoH* cg = nullptr, const XSegs* xs = nullptr,
+                   const GegluH* gg = nullptr) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   if (xs) p.kseg = xs->cols / 64;
+  if (gg) { p.geglu = gg->d_ff; p.geglu_store_y = gg->store_y; }
   if (cg) {
     p.conv = 1; p.cv_S = cg->S; p.cv_cpb = (cg->C + 63) / 64; p.cv_Ho = cg->Ho; p.cv_Wo = cg->Wo;
     p.cv_pad_h = cg->pad_h; p.cv_pad_w = cg->pad_w; p.cv_str_h = cg->str_h; p.cv_str_w = cg->str_w;
@@ -337,6 +342,11 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   p.BN = tc_pick_bn(M, Kc, Nout, 256, dev_info().sms / 2);
   p.num_m_blk = (int)((M + 255) / 256);
   p.num_n_blk = (Nout + p.BN - 1) / p.BN;
+  if (gg) {     // a tile = 64 hidden + 64 gate columns (chunk pairs of the epilogue are 32 wide); no pre-wait W loads
+    p.BN = 128;
+    p.num_n_blk = gg->d_ff / (p.BN / 2);
+    p.w_prefetch = 0;
+  }
   p.num_k_blk = (Kc + 63) / 64;
   const int smem = tc2_smem_bytes(p.BN, &p.stages);
   if (p.stages < 2) { set_error("tc2: not enough shared memory for BN=%d", p.BN); return B200LORA_E_SHAPE; }
@@ -368,6 +378,15 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   } else if ((rc = get_tmap(&tmX, X, (uint64_t)M, (uint64_t)Kc, (uint64_t)ldx, 128, 64, io_dtype,
                             CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if (!xs) { tmX1 = tmX; tmX2 = tmX; }
+  CUtensorMap tmOut;
+  if (gg) {     // hidden rows: [BN/2 x 64] boxes; the leader's first 8 gate rows: [8 x 64] boxes
+    if ((rc = get_tmap(&tmX1, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)(p.BN / 2), 64, io_dtype,
+                       CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    if ((rc = get_tmap(&tmX2, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, 8, 64, io_dtype,
+                       CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    if ((rc = get_tmap(&tmOut, gg->out, (uint64_t)M, (uint64_t)gg->d_ff, (uint64_t)gg->ldo, 32, 32, io_dtype,
+                       CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  }
   if ((rc = get_tmap(&tmWa, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)(H - 16), 64,
                      io_dtype, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmWb, W, (uint64_t)Nout, (uint64_t)Kc, (uint64_t)ldw, (uint32_t)H, 64, io_dtype,
@@ -376,11 +395,13 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if ((rc = get_tmap(&tmS2, S2_pack, (uint64_t)Nout, 64, 64, (uint32_t)(p.BN / 2), 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
-  if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
-                     CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  if (gg && !gg->store_y) tmY = tmOut;      // (no pre-activation wanted: the map is never used)
+  else if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
+                          CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  if (!gg) tmOut = tmY;
   cudaError_t e = io_dtype == B200LORA_BF16
-                      ? launch_tc2<__nv_bfloat16>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream)
-                      : launch_tc2<__half>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem, stream);
+                      ? launch_tc2<__nv_bfloat16>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem, stream)
+                      : launch_tc2<__half>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem, stream);
   if (e != cudaSuccess) {
     if (!g_err[0]) set_error("tc2 launch failed: %s", cudaGetErrorString(e));
     return B200LORA_E_CUDA;
@@ -570,6 +591,43 @@ extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layou
   const void* s2p = pk ? pk + 2ll * (16 * ((int64_t)K + N) + 64ll * N) : nullptr;
   return b200lora_lora_gemm(dY, N, W, ldw, w_layout, nullptr, 0, B, 1, r, s1p, A, 1, K, ab_dtype,
                             s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
+}
+
+// GEGLU projection with the activation in the epilogue: W0 = [hidden ; gate] rows [2*d_ff, K];
+// out = hidden * gelu(gate) [M, d_ff]; Y [M, 2*d_ff] (the pre-activation, what the backward needs) is optional.
+extern "C" int b200lora_linear_fwd_geglu(const void* X, const void* W0, const void* pack, int has_bias, float scale,
+                                         void* Y, void* out, void* T_out, int64_t M, int K, int d_ff, int r,
+                                         int io_dtype, b200lora_stream_t stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  g_err[0] = 0;
+  if (!X || !W0 || !pack || !out) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("the GEGLU epilogue is 16-bit io only"); return B200LORA_E_DTYPE; }
+  if (d_ff < 64 || d_ff % 64) { set_error("the GEGLU epilogue needs d_ff %% 64 == 0 (got %d)", d_ff); return B200LORA_E_SHAPE; }
+  if (r < 1 || r > 16) { set_error("the GEGLU epilogue supports 1 <= r <= 16 (got %d)", r); return B200LORA_E_SHAPE; }
+  if (M <= 0) return 0;
+  const int N = 2 * d_ff;
+  if (!use_pair()) { set_error("the GEGLU epilogue lives in the CTA-pair kernel (B200LORA_PAIR=0 is set)"); return B200LORA_E_ARG; }
+  if (!tc_applicable(X, K, W0, K, B200LORA_W_NK, Y ? Y : out, Y ? N : d_ff, r, io_dtype, K) || !aligned16(out) || (d_ff % 8)) return B200LORA_E_ALIGN;
+  const char* pk = reinterpret_cast<const char*>(pack);
+  const void* s1p = pk;
+  const void* s2p = pk + 2ll * 16 * ((int64_t)K + N);
+  GegluH gg{d_ff, out, d_ff, Y ? 1 : 0};
+  return run_tc2(X, K, W0, K, has_bias != 0, s1p, s2p, scale, Y, N, T_out, M, K, N, r, io_dtype, stream, nullptr, nullptr, &gg);
+}
+
+extern "C" int b200lora_geglu_bwd(const void* dout, const void* Y, void* dY, int64_t M, int d_ff, int io_dtype,
+                                  b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!dout || !Y || !dY) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (!valid_dtype(io_dtype)) { set_error("bad dtype enum"); return B200LORA_E_DTYPE; }
+  const int vec = 16 / dtype_size(io_dtype);
+  if (d_ff < 1 || d_ff % vec) { set_error("geglu_bwd needs d_ff %% %d == 0", vec); return B200LORA_E_SHAPE; }
+  if (!aligned16(dout) || !aligned16(Y) || !aligned16(dY)) { set_error("geglu_bwd needs 16-byte aligned pointers"); return B200LORA_E_ALIGN; }
+  if (M <= 0) return 0;
+  DevInfo di = dev_info();
+  cudaError_t e = launch_geglu_bwd(dout, Y, dY, M, d_ff, io_dtype, di.sms > 0 ? di.sms : 148, reinterpret_cast<cudaStream_t>(stream_));
+  if (e != cudaSuccess) { set_error("geglu_bwd launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
+  return 0;
 }
 
 // =========================================================================================

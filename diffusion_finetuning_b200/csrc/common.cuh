@@ -53,6 +53,10 @@ struct TcParams {
   int kseg;                   // != 0: X is split along K into tensors of kseg k-blocks each (<= 3)
   int cluster_scope;          // pair kernel: release.cluster / acquire.cluster on the cross-CTA hand-offs (default 1)
   int w_prefetch;             // pair kernel: request the first stages' W half-tiles before griddepcontrol.wait
+  int geglu;                  // pair kernel, != 0: W is [2*geglu, K] = [hidden ; gate] (GEGLU projection); a tile covers BN/2
+                              // hidden columns and the BN/2 gate columns of the same outputs, the epilogue also writes
+                              // hidden * gelu(gate) [M, geglu] (tmOut); Nout = 2*geglu, num_n_blk counts BN/2-wide blocks
+  int geglu_store_y;          // ... and still stores the pre-activation Y [M, 2*geglu] (needed by the backward)
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;
 };

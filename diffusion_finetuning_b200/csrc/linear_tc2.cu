@@ -88,7 +88,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                      const __grid_constant__ CUtensorMap tmX2, const __grid_constant__ CUtensorMap tmWa,
                      const __grid_constant__ CUtensorMap tmWh, const __grid_constant__ CUtensorMap tmS1,
                      const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmY,
-                     const TcParams p) {
+                     const __grid_constant__ CUtensorMap tmOut, const TcParams p) {
   using namespace tc2;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -142,6 +142,11 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
     tma_prefetch_desc(&tmS1);
     tma_prefetch_desc(&tmS2);
     tma_prefetch_desc(&tmY);
+    if (p.geglu) {
+      tma_prefetch_desc(&tmX1);      // GEGLU mode: W with a [BN/2 x 64] box (hidden rows)
+      tma_prefetch_desc(&tmX2);      //             W with an [8 x 64] box (first gate rows of the leader's half)
+      tma_prefetch_desc(&tmOut);
+    }
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -242,6 +247,18 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                 tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
               else     // X split along K into equal segments, one tensor each (fused sibling backward)
                 tma_load_2d_2sm(a_dst, xm, full0, sk * BK, m_blk * 256 + (int)rank * BM, pol_x);
+            } else if (p.geglu) {
+              // GEGLU projection: B rows of the pair = [hidden j0 .. j0+BN/2) ; gate j0 .. j0+BN/2) ; 16 rank rows].
+              // The leader's half (H = BN/2 + 8 rows) is the hidden rows plus the first 8 gate rows (two boxes), the
+              // peer's the other BN/2 - 8 gate rows (= H - 16: the usual box) and the rank rows.
+              const int j0 = n_blk * (BN / 2);
+              if (leader) {
+                tma_load_2d_2sm(b_dst, &tmX1, full0, kb * BK, j0, pol_w);
+                tma_load_2d_2sm(b_dst + (size_t)(BN / 2) * 128, &tmX2, full0, kb * BK, p.geglu + j0, pol_w);
+              } else {
+                tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, p.geglu + j0 + 8, pol_w);
+                tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
+              }
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
               if (kb >= w_done) tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);   // H rows
@@ -265,7 +282,9 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             if (leader) mbar_arrive_expect_tx(&full_bar[s], tail_tx);
             else mbar_arrive_cluster(full0);
           } else {
-            tma_load_2d_2sm(b_dst, &tmS2, full0, 0, n_blk * BN + (int)rank * (BN / 2), pol_w);
+            const int s2_row = p.geglu ? n_blk * (BN / 2) + (int)rank * p.geglu      // leader: hidden rows, peer: gate rows
+                                       : n_blk * BN + (int)rank * (BN / 2);
+            tma_load_2d_2sm(b_dst, &tmS2, full0, 0, s2_row, pol_w);
           }
         }
         __syncwarp();
@@ -567,6 +586,57 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         }
         released = true;
       };
+      if (p.geglu) {
+        // ---- GEGLU projection: accumulator columns [0, BN/2) = hidden, [BN/2, BN) = gate of the same BN/2 outputs.
+        // This warp takes the 32-column chunk pairs pi = half, half + 2, ...: out = hidden * gelu(gate), rounded as the
+        // reference composition rounds (projection output, gelu, product: each a tensor of the io dtype), stored
+        // to tmOut [M, geglu]; the pre-activation chunks go to Y [M, 2*geglu] when the backward needs them.
+        const int np = BN / (2 * EPI_COLS);
+        const int j0 = n_blk * (BN / 2);
+        const int row0 = m_blk * 256 + (int)rank * BM + qd * 32;
+        int last_pi = -1;
+        for (int pi = half; pi < np; pi += 2)
+          if (j0 + pi * EPI_COLS < p.geglu) last_pi = pi;
+        auto emit = [&](const uint32_t (&w)[32], const CUtensorMap* tm, int col) {
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          const uint32_t dst = stg_row + buf * (32 * EPI_COLS * 2);
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            st_shared_v4(dst + ((q ^ wr_sw) << 4),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 0]), __uint_as_float(w[q * 8 + 1])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 2]), __uint_as_float(w[q * 8 + 3])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 4]), __uint_as_float(w[q * 8 + 5])),
+                         pack2b<TIO>(__uint_as_float(w[q * 8 + 6]), __uint_as_float(w[q * 8 + 7])));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(tm, my_staging + buf * (32 * EPI_COLS * 2), col, row0);
+            tma_store_commit();
+          }
+          buf ^= 1;
+        };
+        for (int pi = half; pi < np; pi += 2) {
+          if (j0 + pi * EPI_COLS >= p.geglu) continue;
+          tmem_ld_x32(acc_addr + pi * EPI_COLS, v[0]);
+          tmem_ld_x32(acc_addr + (np + pi) * EPI_COLS, v[1]);
+          tmem_ld_wait_dep(v[0]);
+          tmem_ld_wait_dep(v[1]);
+          if (pi == last_pi) release_stage();
+          if (p.geglu_store_y) {
+            emit(v[0], &tmY, j0 + pi * EPI_COLS);
+            emit(v[1], &tmY, p.geglu + j0 + pi * EPI_COLS);
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float h = to_f32(from_f32<TIO>(__uint_as_float(v[0][i])));
+            const float g = to_f32(from_f32<TIO>(__uint_as_float(v[1][i])));
+            const float ge = to_f32(from_f32<TIO>(0.5f * g * (1.0f + erff(g * 0.70710678118654752f))));
+            v[0][i] = __float_as_uint(h * ge);
+          }
+          emit(v[0], &tmOut, j0 + pi * EPI_COLS);
+        }
+      } else
 #pragma unroll
       for (int ci = 0; ci < MAX_CI; ++ci) {
         const int c = 2 * ci + half;
@@ -637,8 +707,8 @@ template <typename TIO, bool DBG>
 static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CUtensorMap& tmX2,
                                    const CUtensorMap& tmWa,
                                    const CUtensorMap& tmWb, const CUtensorMap& tmS1,
-                                   const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p,
-                                   int smem_bytes, cudaStream_t stream) {
+                                   const CUtensorMap& tmS2, const CUtensorMap& tmY, const CUtensorMap& tmOut,
+                                   const TcParams& p, int smem_bytes, cudaStream_t stream) {
   auto kern = lora_gemm_tc2_kernel<TIO, DBG>;
   // The opt-in smem cap is a process-wide attribute of the function: raise it ONCE to the device
   // maximum (autograd runs the backward on another thread — a per-thread cache of "what I last
@@ -681,7 +751,7 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
   const int num_tiles = p.num_m_blk * p.num_n_blk;
   const int ncl = num_tiles < max_clusters ? num_tiles : max_clusters;
   cfg.gridDim = dim3(2 * ncl, 1, 1);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p);
   if (e != cudaSuccess)
     set_error("tc2: cudaLaunchKernelEx(grid=%d, smem=%d, BN=%d, stages=%d): %s", 2 * ncl, smem_bytes, p.BN,
               p.stages, cudaGetErrorString(e));
@@ -691,20 +761,20 @@ static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tm
 template <typename TIO>
 cudaError_t launch_tc2(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CUtensorMap& tmX2,
                        const CUtensorMap& tmWa, const CUtensorMap& tmWb, const CUtensorMap& tmS1,
-                       const CUtensorMap& tmS2, const CUtensorMap& tmY, const TcParams& p, int smem_bytes,
-                       cudaStream_t stream) {
+                       const CUtensorMap& tmS2, const CUtensorMap& tmY, const CUtensorMap& tmOut, const TcParams& p,
+                       int smem_bytes, cudaStream_t stream) {
   if (p.dbg != nullptr)
-    return launch_tc2_impl<TIO, true>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
-  return launch_tc2_impl<TIO, false>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, p, smem_bytes, stream);
+    return launch_tc2_impl<TIO, true>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
+  return launch_tc2_impl<TIO, false>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
 }
 
 template cudaError_t launch_tc2<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                                                const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                                               const CUtensorMap&, const CUtensorMap&, const TcParams&, int,
-                                               cudaStream_t);
+                                               const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
+                                               const TcParams&, int, cudaStream_t);
 template cudaError_t launch_tc2<__half>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
                                         const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
-                                        const CUtensorMap&, const CUtensorMap&, const TcParams&, int,
-                                        cudaStream_t);
+                                        const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const TcParams&,
+                                        int, cudaStream_t);
 
 }  // namespace b200

@@ -291,3 +291,44 @@ def unfuse_sibling_projections(model):
     for m in model.modules():
         if getattr(m, "_sibling_group", None) is not None:
             m._sibling_group = None
+
+
+# ---------------------------------------------------------------------------------------------
+# GEGLU: activation in the projection kernel's epilogue
+# ---------------------------------------------------------------------------------------------
+def fuse_geglu(model, class_names=("GEGLU",)):
+    """Route every `GEGLU` module whose `proj` is a LoraInjectedLinear through `proj.forward_geglu`: the module's
+    `hidden, gate = proj(x).chunk(2, dim=-1); hidden * gelu(gate)` becomes ONE kernel in the forward (the activation
+    rides in the GEMM epilogue; the `[M, 2*d_ff]` pre-activation is only written when a backward will read it) and
+    one elementwise kernel + the layer's usual backward in the backward.  Calls the fused path cannot take (fp32
+    compute, active dropout, d_ff % 64 != 0) fall through to the module's own forward.  Returns the patched modules."""
+    from .lora import LoraInjectedLinear
+    patched = []
+    for m in model.modules():
+        if type(m).__name__ not in class_names or not isinstance(getattr(m, "proj", None), LoraInjectedLinear):
+            continue
+        if getattr(m, "_b200_geglu_orig", None) is not None:
+            patched.append(m)
+            continue
+        orig = m.forward
+
+        def forward(x, *args, _m=m, _orig=orig, **kwargs):
+            out = _m.proj.forward_geglu(x) if not args and not kwargs else None
+            if out is None:
+                return _orig(x, *args, **kwargs)
+            _m.fused_calls = getattr(_m, "fused_calls", 0) + 1
+            return out
+
+        m._b200_geglu_orig = orig
+        m.forward = forward
+        patched.append(m)
+    return patched
+
+
+def unfuse_geglu(model):
+    for m in model.modules():
+        orig = getattr(m, "_b200_geglu_orig", None)
+        if orig is not None:
+            m.forward = orig
+            m._b200_geglu_orig = None
+

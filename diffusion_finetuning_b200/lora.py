@@ -108,6 +108,20 @@ class LoraInjectedLinear(nn.Module):
         return ops.lora_linear(input, self.linear.weight, self.linear.bias, A, B, self.scale,
                                cache=self._base_cache, sink=sink)
 
+    def forward_geglu(self, input):
+        """`h, g = self(input).chunk(2, dim=-1); h * gelu(g)` — what a `GEGLU` module does around this layer when it is
+        the module's `proj` (reference lora.py:53 lists GEGLU among the default targets) — with the activation applied in
+        the projection kernel's epilogue.  Returns None when this call cannot take that path (dropout on the branch,
+        sibling fusion, fp32 compute, odd sizes): the caller then runs the unfused composition."""
+        if self._sibling_group is not None or (self.training and self.dropout.p > 0.0) or _TORCH_OP_ROUTE:
+            return None
+        A = self._down_weight()
+        if not ops.geglu_fusable(input, self.linear.weight, A):
+            return None
+        sink = self._grad_sink if A is self.lora_down.weight else None
+        return ops.lora_linear_geglu(input, self.linear.weight, self.linear.bias, A, self.lora_up.weight, self.scale,
+                                     cache=self._base_cache, sink=sink)
+
     def realize_as_lora(self):
         return self.lora_up.weight.data * self.scale, self.lora_down.weight.data
 

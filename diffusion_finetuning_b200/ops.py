@@ -169,7 +169,7 @@ class _LoraLinearFn(torch.autograd.Function):
     """y = x·W0ᵀ + b + s·(x·Aᵀ)·Bᵀ as ONE kernel; backward = fused dX kernel + token reductions."""
 
     @staticmethod
-    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic, sink=None, grad_on=True):
+    def forward(ctx, x, w0, bias, A, B, scale, cache, impl, deterministic, sink=None, grad_on=True, geglu=False):
         nat.require_cuda(x, "LoraInjectedLinear.forward")
         for name, t in (("linear.weight", w0), ("lora_down.weight", A), ("lora_up.weight", B)):
             if t.device != x.device:
@@ -204,12 +204,25 @@ class _LoraLinearFn(torch.autograd.Function):
         use_tc = _tc_ok(cdt, K, N, r, x.device, impl)
         # needs_input_grad reflects requires_grad only; `grad_on` is the grad mode at apply time
         need_grad = grad_on and any(ctx.needs_input_grad[i] for i in (0, 1, 2, 3, 4))
-        y = torch.empty((M, N), dtype=cdt, device=x.device)
+        # geglu: w0 is a GEGLU projection [2*d_ff, K]; the kernel's epilogue also writes hidden * gelu(gate) [M, d_ff].
+        # The pre-activation y is only materialised when a backward will read it.
+        y = torch.empty((M, N), dtype=cdt, device=x.device) if (need_grad or not geglu) else None
         T = torch.empty((M, r), dtype=cdt, device=x.device) if need_grad else None
         pack = None
         if use_tc and M > 0:
             pack = cache.lora_pack(A, B, bias, cdt, live=grad_on and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]))
-        if M > 0:
+        out = None
+        if geglu:
+            if not use_tc:
+                raise nat.B200LoraError("the GEGLU epilogue needs the tcgen05 path (lora_linear_geglu checks this)")
+            out = torch.empty((M, N // 2), dtype=cdt, device=x.device)
+            if M > 0:
+                with torch.cuda.device(x.device), _Prof("fwd", M, K, N, r, x2.element_size()):
+                    rc = lib.b200lora_linear_fwd_geglu(nat.ptr(x2), nat.ptr(w), nat.ptr(pack), 1 if bc is not None else 0,
+                                                       float(scale), nat.ptr(y), nat.ptr(out), nat.ptr(T), M, K, N // 2, r,
+                                                       nat.dtype_code(cdt), nat.stream_ptr(x.device))
+                    nat.check(rc, "b200lora_linear_fwd_geglu")
+        elif M > 0:
             with torch.cuda.device(x.device), _Prof("fwd", M, K, N, r, x2.element_size()):
                 rc = lib.b200lora_linear_fwd(
                     nat.ptr(x2), nat.ptr(w), nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
@@ -221,11 +234,17 @@ class _LoraLinearFn(torch.autograd.Function):
             ctx.save_for_backward(x2, T, A, B, w0, w)
             ctx.meta = (lead, M, K, N, r, float(scale), cdt, use_tc, cache, bool(deterministic),
                         x.dtype, bias is not None, pack, sink)
+        if geglu:
+            out = out.reshape(*lead, N // 2)
+            if y is None:
+                return out
+            ctx.mark_non_differentiable(out)
+            return y.reshape(*lead, N), out
         return y.reshape(*lead, N)
 
     @staticmethod
     @torch.autograd.function.once_differentiable
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dout=None):
         x2, T, A, B, w0, w = ctx.saved_tensors
         (lead, M, K, N, r, scale, cdt, use_tc, cache, deterministic, x_dtype, has_bias, pack,
          sink) = ctx.meta
@@ -302,7 +321,7 @@ class _LoraLinearFn(torch.autograd.Function):
                 dx = dx.to(x_dtype)
         else:
             dx = None
-        return dx, dW, db, dA, dB, None, None, None, None, None, None
+        return dx, dW, db, dA, dB, None, None, None, None, None, None, None
 
 
 def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None,
@@ -315,6 +334,61 @@ def lora_linear(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, d
         deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
     return _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic,
                                sink, torch.is_grad_enabled())
+
+
+class _GegluAct(torch.autograd.Function):
+    """The autograd node between the pre-activation `y` = [hidden | gate] and `out` = hidden * gelu(gate), which the
+    GEMM epilogue has ALREADY computed: forward hands `out` through (no launch), backward is one elementwise kernel
+    (b200lora_geglu_bwd) whose result feeds the layer's usual backward."""
+
+    @staticmethod
+    def forward(ctx, y, out):
+        ctx.save_for_backward(y)
+        return out.view_as(out)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, dout):
+        (y,) = ctx.saved_tensors
+        lib = nat.lib()
+        d_ff = y.shape[-1] // 2
+        y2 = y.reshape(-1, 2 * d_ff)
+        do2 = dout.reshape(-1, d_ff)
+        if do2.dtype != y2.dtype:
+            do2 = do2.to(y2.dtype)
+        do2 = do2.contiguous()
+        dy = torch.empty_like(y2)
+        if y2.shape[0] > 0:
+            with torch.cuda.device(y.device):
+                nat.check(lib.b200lora_geglu_bwd(nat.ptr(do2), nat.ptr(y2), nat.ptr(dy), y2.shape[0], d_ff,
+                                                 nat.dtype_code(y2.dtype), nat.stream_ptr(y.device)), "b200lora_geglu_bwd")
+        return dy.reshape(y.shape), None
+
+
+def geglu_fusable(x, w0, lora_down, impl=None):
+    """Can `hidden, gate = proj(x).chunk(2, -1); hidden * gelu(gate)` run with the activation in the GEMM epilogue?
+    (16-bit compute dtype on the CTA-pair tcgen05 kernel, d_ff % 64 == 0, rank <= 16.)"""
+    if not x.is_cuda or os.environ.get("B200LORA_PAIR", "1") == "0":
+        return False
+    N, K = w0.shape
+    r = lora_down.shape[0]
+    cdt = _compute_dtype(x, w0)
+    return N % 128 == 0 and r <= 16 and _tc_ok(cdt, K, N, r, x.device, _impl_from_env() if impl is None else impl)
+
+
+def lora_linear_geglu(x, w0, bias, lora_down, lora_up, scale, cache=None, impl=None, deterministic=None, sink=None):
+    """`h, g = lora_linear(x, ...).chunk(2, dim=-1); h * gelu(g)` (the GEGLU module around reference lora.py:49-50) with
+    the activation applied in the projection kernel's epilogue (b200lora_linear_fwd_geglu).  Call `geglu_fusable` first."""
+    if impl is None:
+        impl = _impl_from_env()
+    if deterministic is None:
+        deterministic = os.environ.get("B200LORA_DETERMINISTIC", "0") == "1"
+    res = _LoraLinearFn.apply(x, w0, bias, lora_down, lora_up, scale, cache, impl, deterministic, sink,
+                              torch.is_grad_enabled(), True)
+    if isinstance(res, tuple):
+        y, out = res
+        return _GegluAct.apply(y, out)
+    return res
 
 
 # --------------------------------------------------------------------------------------------

@@ -613,7 +613,7 @@ def main(argv=None):
     torch.cuda.set_device(device)
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
-    from .fused import fuse_sibling_projections
+    from .fused import fuse_geglu, fuse_sibling_projections
     from .unet_sd15 import UNet2DConditionModel
     cfg = TrainConfig(**{f.name: getattr(a, f.name) for f in dataclasses.fields(TrainConfig)})
     if a.extended and cfg.mixed_precision == "no" and int(os.environ.get("RANK", "0")) == 0:
@@ -626,6 +626,7 @@ def main(argv=None):
     inject(unet, r=a.lora_rank)
     if a.fuse_siblings:
         fuse_sibling_projections(unet)
+        fuse_geglu(unet)             # no-op unless GEGLU projections are injected (default / extended targets)
     tr = LoraTrainer(unet, cfg)
     res = a.resolution // 8
     ctx_dim = 32 if a.tiny else 768

@@ -237,6 +237,23 @@ int b200lora_lora_grads_static(const void* dY, const void* X, const void* T, con
                                b200lora_stream_t stream);
 
 /*
+ * GEGLU projection with the activation in the GEMM epilogue — replaces, for a LoRA-injected
+ * `GEGLU.proj` (lora.py:53 lists GEGLU among the default targets), the caller's
+ *     hidden, gate = proj(x).chunk(2, dim=-1); out = hidden * gelu(gate)
+ * around lora.py:49-50.  W0 is proj's weight [2*d_ff, K] (hidden rows first), pack as for b200lora_linear_fwd with
+ * N = 2*d_ff.  out [M, d_ff] = hidden * gelu(gate) with the reference's intermediate roundings; Y [M, 2*d_ff] (the
+ * pre-activation, needed by the backward) is written when non-NULL; T [M, r] as in b200lora_linear_fwd.
+ * 16-bit io, d_ff % 64 == 0, 1 <= r <= 16, CTA-pair kernel only (everything else: run the unfused composition).
+ * b200lora_geglu_bwd: dY [M, 2*d_ff] = [dout * gelu(gate) | dout * hidden * gelu'(gate)] in one pass over dout and Y
+ * (the autograd of the two caller-side ops); dY then feeds b200lora_linear_bwd_dx / b200lora_lora_grads unchanged.
+ */
+int b200lora_linear_fwd_geglu(const void* X, const void* W0, const void* pack, int has_bias, float scale,
+                              void* Y, void* out, void* T_out, int64_t M, int K, int d_ff, int r,
+                              int io_dtype, b200lora_stream_t stream);
+int b200lora_geglu_bwd(const void* dout, const void* Y, void* dY, int64_t M, int d_ff, int io_dtype,
+                       b200lora_stream_t stream);
+
+/*
  * Fused sibling projections — layers that evaluate lora.py:49-50 on the SAME input (the to_q / to_k /
  * to_v of one attention block, all called on `hidden_states` by the caller of LoraInjectedLinear)
  * run as ONE problem over their concatenated outputs.

@@ -1,0 +1,157 @@
+"""GEGLU projection with the activation in the GEMM epilogue: a LoRA-injected `GEGLU.proj`
+(reference lora.py:53 lists GEGLU among the default targets; lora.py:49-50 is the layer) followed by the caller's
+`hidden, gate = y.chunk(2, dim=-1); hidden * gelu(gate)`, as ONE kernel (b200lora_linear_fwd_geglu) plus one
+elementwise backward kernel (b200lora_geglu_bwd).  Oracle: the reference composition in fp32 on the CPU, on the
+same (rounded) operands; tolerance 2e-2 on outputs (BASELINE's bf16 bar), 5e-2 on the token-reduced gradients."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+import diffusion_finetuning_b200 as L
+from conftest import rel_err, max_abs_err
+from diffusion_finetuning_b200 import _native as nat
+from diffusion_finetuning_b200 import ops
+from diffusion_finetuning_b200.unet_sd15 import GEGLU
+from oracle import lora_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _module(K, d_ff, r, dtype, seed=0):
+    torch.manual_seed(seed)
+    m = torch.nn.Sequential(GEGLU(K, d_ff)).to(DEV).to(dtype)
+    m.requires_grad_(False)
+    L.inject_trainable_lora(m, {"GEGLU"}, r=r)
+    lin = m[0].proj
+    assert isinstance(lin, L.LoraInjectedLinear)
+    with torch.no_grad():
+        lin.lora_up.weight.normal_(0, 0.05)
+    lin.scale = 0.8
+    return m, lin
+
+
+def _oracle(lin, x, dout):
+    c = lambda t: None if t is None else t.detach().float().cpu()
+    xr = c(x).requires_grad_(True)
+    A = c(lin.lora_down.weight).requires_grad_(True)
+    B = c(lin.lora_up.weight).requires_grad_(True)
+    y = O.lora_linear_forward(xr, c(lin.linear.weight), c(lin.linear.bias), A, B, lin.scale)
+    h, g = y.chunk(2, dim=-1)
+    out = h * F.gelu(g)
+    out.backward(c(dout))
+    return out.detach(), xr.grad, A.grad, B.grad
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(2048, 320, 1280, 4), (777, 320, 1280, 16), (4096, 640, 2560, 4), (130, 1280, 5120, 8)])
+def test_fused_geglu_matches_oracle(shape, dtype):
+    M, K, d_ff, r = shape
+    m, lin = _module(K, d_ff, r, dtype)
+    g = torch.Generator(DEV).manual_seed(3)
+    x = (torch.randn(2, M // 2 if M % 2 == 0 else M, K, device=DEV, generator=g) * (1.0 if M % 2 == 0 else 1.0)).to(dtype)
+    if M % 2:
+        x = x[:1]
+    x.requires_grad_(True)
+    dout = torch.randn(*x.shape[:-1], d_ff, device=DEV, generator=g).to(dtype)
+    # unfused: our layer + the module's own chunk / gelu / mul
+    out_u = m(x)
+    out_u.backward(dout)
+    gu = (x.grad.clone(), lin.lora_down.weight.grad.clone(), lin.lora_up.weight.grad.clone())
+    x.grad = None
+    lin.lora_down.weight.grad = None
+    lin.lora_up.weight.grad = None
+    patched = L.fuse_geglu(m)
+    assert patched == [m[0]]
+    n0 = nat.LAUNCHES
+    out_f = m(x)
+    assert m[0].fused_calls == 1
+    out_f.backward(dout)
+    launches = nat.LAUNCHES - n0
+    out_o, dx_o, dA_o, dB_o = _oracle(lin, x, dout)
+    assert out_f.shape == out_u.shape == (*x.shape[:-1], d_ff) and out_f.dtype == dtype
+    assert rel_err(out_f, out_o) < 2e-2, rel_err(out_f, out_o)
+    assert rel_err(out_f, out_u) < 1e-2                      # same roundings, different accumulation order only
+    assert max_abs_err(out_f, out_o) < 0.05 * out_o.abs().max().item() + 1e-3
+    assert rel_err(x.grad, dx_o) < 3e-2, rel_err(x.grad, dx_o)
+    assert rel_err(lin.lora_down.weight.grad, dA_o) < 5e-2, rel_err(lin.lora_down.weight.grad, dA_o)
+    assert rel_err(lin.lora_up.weight.grad, dB_o) < 5e-2, rel_err(lin.lora_up.weight.grad, dB_o)
+    assert rel_err(x.grad, gu[0]) < 2e-2 and rel_err(lin.lora_up.weight.grad, gu[2]) < 3e-2
+    # pack (training: every call) + fused forward, then geglu_bwd + dX kernel + reductions
+    assert launches <= 6, launches
+    # without autograd the pre-activation is never written: same `out`, one launch fewer tensors
+    with torch.no_grad():
+        out_n = m(x)
+    assert torch.equal(out_n, out_f.detach())
+    L.unfuse_geglu(m)
+    assert rel_err(m(x), out_u) == 0.0
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2), (torch.float16, 5e-3)])
+def test_geglu_bwd_kernel_matches_autograd(dtype, tol):
+    M, d_ff = 1000, 320
+    g = torch.Generator(DEV).manual_seed(5)
+    y = (torch.randn(M, 2 * d_ff, device=DEV, generator=g) * 1.5).to(dtype)
+    dout = torch.randn(M, d_ff, device=DEV, generator=g).to(dtype)
+    dy = torch.empty_like(y)
+    nat.check(nat.lib().b200lora_geglu_bwd(nat.ptr(dout), nat.ptr(y), nat.ptr(dy), M, d_ff, nat.dtype_code(dtype),
+                                           nat.stream_ptr(torch.device(DEV))), "b200lora_geglu_bwd")
+    yr = y.detach().double().cpu().requires_grad_(True)
+    h, gt = yr.chunk(2, dim=-1)
+    (h * F.gelu(gt)).backward(dout.double().cpu())
+    assert rel_err(dy, yr.grad.float()) < tol, rel_err(dy, yr.grad.float())
+
+
+def test_fp32_and_odd_sizes_fall_through_to_the_module():
+    m, lin = _module(320, 1280, 4, torch.float32)
+    L.fuse_geglu(m)
+    x = torch.randn(3, 50, 320, device=DEV)
+    out = m(x)
+    assert getattr(m[0], "fused_calls", 0) == 0              # fp32 compute: the SIMT family has no GEGLU epilogue
+    ref, *_ = _oracle(lin, x, torch.zeros_like(out))
+    assert rel_err(out, ref) < 1e-5
+    m2, _ = _module(64, 96, 4, torch.bfloat16)                # d_ff % 64 != 0
+    L.fuse_geglu(m2)
+    m2(torch.randn(5, 64, device=DEV, dtype=torch.bfloat16))
+    assert getattr(m2[0], "fused_calls", 0) == 0
+
+
+def test_fuse_geglu_on_the_unet_trains_like_the_unfused_model():
+    from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
+
+    def build(fuse):
+        torch.manual_seed(0)
+        unet = UNet2DConditionModel.tiny().to(DEV)
+        unet.requires_grad_(False)
+        torch.manual_seed(1)
+        L.inject_trainable_lora(unet, L.UNET_DEFAULT_TARGET_REPLACE, r=4)
+        gen = torch.Generator().manual_seed(2)
+        with torch.no_grad():
+            for mod in unet.modules():
+                if isinstance(mod, L.LoraInjectedLinear):
+                    mod.lora_up.weight.copy_((torch.randn(mod.lora_up.weight.shape, generator=gen) * 0.02).to(DEV))
+        n = len(L.fuse_geglu(unet)) if fuse else 0
+        return unet, n
+
+    ua, _ = build(False)
+    ub, n = build(True)
+    assert n > 0
+    g = torch.Generator().manual_seed(4)
+    lat = torch.randn(2, 4, 32, 32, generator=g).to(DEV)
+    t = torch.randint(0, 1000, (2,), generator=g).to(DEV)
+    ctx = torch.randn(2, 77, 32, generator=g).to(DEV)
+    losses = []
+    for u in (ua, ub):
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            pred = u(lat, t, ctx)
+        loss = pred.float().square().mean()
+        loss.backward()
+        losses.append(loss.item())
+    fused = [m for m in ub.modules() if type(m).__name__ == "GEGLU"]
+    took = sum(getattr(m, "fused_calls", 0) for m in fused)
+    print(f"GEGLU modules {len(fused)}, fused calls {took}, losses {losses}")
+    assert abs(losses[0] - losses[1]) <= 2e-2 * abs(losses[0])
+    pa = dict(ua.named_parameters())
+    for name, p in ub.named_parameters():
+        if p.requires_grad and p.grad is not None and "ff.net.0.proj" in name:
+            assert rel_err(p.grad, pa[name].grad) < 5e-2, name
