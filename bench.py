@@ -905,6 +905,16 @@ def dp_replica_check(tr, device):
             off += n
         out["differing_per_bucket"] = per_bucket
         out["bucket_sizes"] = [b.hi - b.lo for b in tr.arena.buckets]
+        names = {id(p): n for n, p in tr.unet.named_parameters()} if hasattr(tr, "unet") else {}
+        bad, off = [], 0
+        for p in tr.arena.params:
+            n = p.numel()
+            k = int(diff[off:off + n].sum().item())
+            if k:
+                bad.append({"param": names.get(id(p), "?"), "shape": list(p.shape), "differing": k,
+                            "bucket": tr.arena._slot[id(p)][2]})
+            off += n
+        out["differing_params"] = bad[:16]
     return out
 
 

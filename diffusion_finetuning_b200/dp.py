@@ -130,6 +130,16 @@ class LoraGradArena:
             # (ops.GradSink); it is the ONLY "slice final" signal.  Otherwise autograd accumulated into p.grad
             # (a view of the arena for fp32 parameters; for low-precision parameters the value is folded into
             # the fp32 arena here)
+            # A gradient that came THROUGH autograd (no sink: the LoRA convolutions, low-precision parameters) was
+            # added into p.grad by the AccumulateGrad node on the node's own stream — the stream this hook runs under,
+            # which for a node that outlived a captured step is not the step's stream.  The bucket's event is recorded
+            # on the step's stream, so that stream first waits for the accumulation (found at N = 2 / 8 on config 3:
+            # the `lora_up` factors of five resnet convolutions diverged between replicas under the graph, never eagerly).
+            cs = self._compute_stream
+            if cs is not None:
+                cur = torch.cuda.current_stream(self.device)
+                if cur != cs:
+                    cs.wait_stream(cur)
             if param.dtype != torch.float32:
                 o, n, _ = self._slot[id(param)]
                 with self._on_compute_stream():

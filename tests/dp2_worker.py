@@ -18,21 +18,25 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def build(device, fuse):
+def build(device, fuse, extended=False):
     import diffusion_finetuning_b200 as L
     from diffusion_finetuning_b200.unet_sd15 import UNet2DConditionModel
     torch.manual_seed(0)
     unet = UNet2DConditionModel.tiny().to(device)
     unet.requires_grad_(False)
     torch.manual_seed(1)
-    L.inject_trainable_lora(unet, r=4)
+    if extended:        # resnet convolutions too: their factor gradients come back THROUGH autograd (no GradSink)
+        L.inject_trainable_lora_extended(unet, r=4)
+    else:
+        L.inject_trainable_lora(unet, r=4)
     g = torch.Generator().manual_seed(2)
     with torch.no_grad():
         for m in unet.modules():
-            if isinstance(m, L.LoraInjectedLinear):
+            if isinstance(m, (L.LoraInjectedLinear, L.LoraInjectedConv2d)):
                 m.lora_up.weight.copy_((torch.randn(m.lora_up.weight.shape, generator=g) * 0.02).to(device))
     if fuse:
         L.fuse_sibling_projections(unet)
+        L.fuse_geglu(unet)
     return unet
 
 
@@ -66,9 +70,10 @@ def main():
     per = 2
     full = batch(per * world, 77, device)
     mine = {k: v[rank * per:(rank + 1) * per].contiguous() for k, v in full.items()}
-    for name, autocast, fuse, tol in (("fp32", False, False, 1e-5), ("bf16_fused", True, True, 2e-2)):
+    for name, autocast, fuse, tol, ext in (("fp32", False, False, 1e-5, False), ("bf16_fused", True, True, 2e-2, False),
+                                           ("bf16_extended", True, True, 3e-2, True)):
         # single process, concatenated batch (same seeds on every rank -> same model)
-        ref = build(device, fuse)
+        ref = build(device, fuse, ext)
         ref_arena = dp.LoraGradArena(ref, bucket_bytes=4096, process_group=None)
         ref_arena.world = 1
         ref_arena.zero()
@@ -77,7 +82,7 @@ def main():
         want = ref_arena.flat.clone()
         ref_arena.detach()
         # DP over the shards: eager, buckets fire inside the backward
-        unet = build(device, fuse)
+        unet = build(device, fuse, ext)
         arena = dp.LoraGradArena(unet, bucket_bytes=4096)
         assert len(arena.buckets) > 2
         arena.broadcast_params(0)
@@ -102,11 +107,15 @@ def main():
         torch.cuda.synchronize(device)
         res[name]["graph_rel"] = rel(arena.flat, want)
         res[name]["graph_vs_eager_rel"] = rel(arena.flat, got)
-        # three optimizer steps: replicas stay bit-identical
+        # three eager + three replayed optimizer steps on rank-specific batches: replicas stay bit-identical (the eager
+        # steps run with the captured step's autograd nodes still alive — the stale-stream case of dp.LoraGradArena)
         opt = torch.optim.AdamW(arena.params, lr=1e-3, fused=True)
-        for i in range(3):
+        for i in range(6):
             b = batch(per, 100 + 10 * i + rank, device)
-            step(b)
+            if i < 3:
+                step(b)
+            else:
+                graphed(b)
             arena.clip_grad_norm_(1.0)
             opt.step()
         flat = torch.cat([p.detach().reshape(-1) for p in arena.params]).view(torch.int32)
