@@ -342,9 +342,12 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   p.BN = tc_pick_bn(M, Kc, Nout, 256, dev_info().sms / 2);
   p.num_m_blk = (int)((M + 255) / 256);
   p.num_n_blk = (Nout + p.BN - 1) / p.BN;
-  if (gg) {     // a tile = 64 hidden + 64 gate columns (chunk pairs of the epilogue are 32 wide); no pre-wait W loads
-    p.BN = 128;
-    p.num_n_blk = gg->d_ff / (p.BN / 2);
+  if (gg) {     // a tile = BN/2 hidden + BN/2 gate columns (chunk pairs of the epilogue are 32 wide: BN % 64 == 0); the
+                // last tile may be ragged (the epilogue masks chunk pairs beyond d_ff); no pre-wait W loads
+    static int gbn = -1;
+    if (gbn < 0) { const char* e = getenv("B200LORA_GEGLU_BN"); gbn = e ? atoi(e) : 128; if (gbn != 64 && gbn != 128 && gbn != 192) gbn = 128; }
+    p.BN = gbn;
+    p.num_n_blk = (gg->d_ff + p.BN / 2 - 1) / (p.BN / 2);
     p.w_prefetch = 0;
   }
   p.num_k_blk = (Kc + 63) / 64;
@@ -602,7 +605,7 @@ extern "C" int b200lora_linear_fwd_geglu(const void* X, const void* W0, const vo
   g_err[0] = 0;
   if (!X || !W0 || !pack || !out) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("the GEGLU epilogue is 16-bit io only"); return B200LORA_E_DTYPE; }
-  if (d_ff < 64 || d_ff % 64) { set_error("the GEGLU epilogue needs d_ff %% 64 == 0 (got %d)", d_ff); return B200LORA_E_SHAPE; }
+  if (d_ff < 64 || d_ff % 32) { set_error("the GEGLU epilogue needs d_ff %% 32 == 0 and d_ff >= 64 (got %d)", d_ff); return B200LORA_E_SHAPE; }
   if (r < 1 || r > 16) { set_error("the GEGLU epilogue supports 1 <= r <= 16 (got %d)", r); return B200LORA_E_SHAPE; }
   if (M <= 0) return 0;
   const int N = 2 * d_ff;
