@@ -187,6 +187,27 @@ def test_merge_batch_streamed_kernel_bit_identical(wdt, ldt, ranks):
     assert [w.data_ptr() for w in dW] == ptrs and all(torch.equal(a, b) for a, b in zip(dW, want))
 
 
+def test_merge_batch_streamed_kernel_table_and_geometry_edges():
+    """Edges of the streamed merge kernel's tiling: more matrices than its shared-memory table mirror holds (192: the
+    table is then walked in global memory), rows of 16 bytes (the rows-per-tile cap), rows longer than a stage (cut into
+    <= 4 KB column blocks, many per row), a single row, fewer tiles than CTAs — each bit-identical to the per-matrix kernel."""
+    g = torch.Generator().manual_seed(9)
+    dims = [(48, 64)] * 200 + [(1000, 8), (3, 20000), (1, 320), (257, 4104)]
+    ranks = [1 + (i % 4) for i in range(len(dims))]
+    for wdt in (torch.float16, torch.float32):
+        Ws = [(torch.randn(N, K, generator=g) * 0.03).to(wdt).to(DEV) for N, K in dims]
+        Us = [(torch.randn(N, r, generator=g) * 0.05).to(wdt).to(DEV) for (N, _), r in zip(dims, ranks)]
+        Ds = [(torch.randn(r, K, generator=g) * 0.3).to(wdt).to(DEV) for (_, K), r in zip(dims, ranks)]
+        got = ops.merge_lora_weights(Ws, Us, Ds, 0.7)
+        for i in list(range(0, 200, 37)) + [200, 201, 202, 203]:
+            single = ops.merge_lora_weight(Ws[i], Us[i], Ds[i], 0.7)
+            assert torch.equal(single, got[i]), (wdt, dims[i], (single.float() - got[i].float()).abs().max().item())
+    # a lone small matrix: fewer tiles than CTAs
+    w = (torch.randn(40, 72, generator=g) * 0.03).to(DEV)
+    u, d = (torch.randn(40, 4, generator=g) * 0.05).to(DEV), (torch.randn(4, 72, generator=g) * 0.3).to(DEV)
+    assert torch.equal(ops.merge_lora_weights([w], [u], [d], 1.0)[0], ops.merge_lora_weight(w, u, d, 1.0))
+
+
 def test_merge_batch_matches_reference_vectors():
     blob, meta = load_golden("merge_cases.safetensors")
     alpha = float(meta["alpha"])
