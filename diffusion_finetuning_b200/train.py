@@ -592,7 +592,7 @@ def main(argv=None):
     ap.add_argument("--resolution", type=int, default=512)
     ap.add_argument("--lora-rank", type=int, default=4)
     ap.add_argument("--extended", action="store_true", help="inject_trainable_lora_extended (resnet convs too)")
-    ap.add_argument("--fuse-siblings", action="store_true", help="q/k/v LoRA layers of a block as one launch")
+    ap.add_argument("--fuse-siblings", action="store_true", help="q/k/v LoRA layers of a block as one launch; GEGLU projections with the activation in the GEMM epilogue")
     for f in dataclasses.fields(TrainConfig):
         flag = "--" + f.name.replace("_", "-")
         if f.type is bool or isinstance(f.default, bool):

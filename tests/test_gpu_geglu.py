@@ -44,7 +44,8 @@ def _oracle(lin, x, dout):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("shape", [(2048, 320, 1280, 4), (777, 320, 1280, 16), (4096, 640, 2560, 4), (130, 1280, 5120, 8)])
+@pytest.mark.parametrize("shape", [(2048, 320, 1280, 4), (777, 320, 1280, 16), (4096, 640, 2560, 4), (130, 1280, 5120, 8),
+                                   (7, 320, 1280, 1), (512, 64, 64, 4)])
 def test_fused_geglu_matches_oracle(shape, dtype):
     M, K, d_ff, r = shape
     m, lin = _module(K, d_ff, r, dtype)
