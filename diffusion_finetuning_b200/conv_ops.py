@@ -24,12 +24,15 @@ def _ceil64(c):
 
 
 def _nhwc(x, dtype):
-    """[N,C,H,W] (any memory format) -> contiguous [N,H,W,C] in `dtype` (zero-copy when `x` is
-    already channels_last in that dtype)."""
+    """[N,C,H,W] (any memory format) -> contiguous [N,H,W,C] in `dtype`: zero-copy when `x` is already channels_last in
+    that dtype, otherwise ONE strided-read / dense-write pass that changes layout and dtype together (`.to(dtype)` on
+    the permuted view keeps the NCHW strides, so cast-then-`.contiguous()` was two passes over the activation)."""
     t = x.permute(0, 2, 3, 1)
-    if t.dtype != dtype:
-        t = t.to(dtype)
-    return t.contiguous()
+    if t.dtype == dtype and t.is_contiguous():
+        return t
+    out = torch.empty(t.shape, dtype=dtype, device=x.device)
+    out.copy_(t)
+    return out
 
 
 class _ConvState:
