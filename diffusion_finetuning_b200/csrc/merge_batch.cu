@@ -326,17 +326,21 @@ lora_merge_batch_kernel(const MergeItem* __restrict__ items, int n_items, int to
 // -----------------------------------------------------------------------------------------------------------------
 // Streamed variant (every rank <= 8): the loads leave the consumers' instruction stream altogether.
 //
-// A tile is R WHOLE ROWS of one matrix (R = what fits 32 KB; rows longer than 32 KB are cut into 32 KB chunks), i.e. ONE
-// contiguous span of W, so one `cp.async.bulk` lands it in shared memory and a second one lands the tile's rows of
-// `up` (also contiguous).  The first version of this kernel kept the [32 rows x 512 bytes] tiles of the kernel above and
-// issued one 512-byte copy per row: 37 copies per 16 KB, and the TMA unit retires a bulk copy every ~80 cycles per SM
-// whatever its size (measured: 2.8-3.4 TB/s, consumers 70 % of the time in the full-barrier wait, no gain from four
-// producer warps) — few large copies is the rule.  One producer warp per CTA walks the CTA's tiles (round-robin over
-// the grid) ahead of the math through a ring of NS stages, completion counted in bytes on the stage's `full` mbarrier;
-// G groups of four consumer warps (3 for fp32 weights, 6 for 16-bit ones) take alternate tiles: a thread owns one 16-byte column of the tile (so its
-// r x VEC slice of `down` stays in registers, fetched from L2 BEFORE the wait on `full`) and walks the rows: LDS.128,
-// rank-r product, rounding chain, coalesced 16-byte store to global.  Bytes in flight are set by the ring (6 x 32 KB per
-// SM), not by registers; the table walk is a forward-only pointer (no search), there is no __syncthreads.
+// A tile is R WHOLE ROWS of one matrix (R = what fits 32 KB, at least 8), i.e. ONE contiguous span of W, so one
+// `cp.async.bulk` lands it in shared memory and a second one lands the tile's rows of `up` (also contiguous); rows longer
+// than 4 KB are cut into equal column blocks of <= 4 KB, 8 rows per tile, one copy per row.  The first version of this
+// kernel kept the [32 rows x 512 bytes] tiles of the kernel above and issued one 512-byte copy per row: 37 copies per
+// 16 KB, and the TMA unit retires a bulk copy every ~80 cycles per SM whatever its size (measured: 2.8-3.4 TB/s,
+// consumers 70 % of the time in the full-barrier wait, no gain from four producer warps) — few large copies is the rule.
+// One producer warp per CTA walks the CTA's tiles ahead of the math through a ring of NS stages, completion counted in
+// bytes on the stage's `full` mbarrier; G groups of four consumer warps (3 for fp32 weights, 6 for 16-bit ones: twice the
+// arithmetic per byte) take alternate tiles.  Within a tile a thread owns one 16-byte column per pass (passes = power-of-
+// two column chunks, so all 128 threads of a group work in every pass): its r x VEC slice of `down` sits in registers
+// (fetched through L1 BEFORE the wait on `full`), it walks the rows with LDS.128, FFMA2 for the rank-r product, the
+// rounding chain, and a coalesced 16-byte store to global.  Bytes in flight are set by the ring (6 x 32 KB per SM), not
+// by registers; the table is mirrored in shared memory and walked by a forward-only pointer (no search); there is no
+// __syncthreads in the loop.  Tiles -> CTAs: round-robin for fp32 weights, contiguous byte-balanced ranges for 16-bit
+// ones (`down` then stays in L1 across a CTA's tiles); both measured, see MS_CONTIG*.
 // -----------------------------------------------------------------------------------------------------------------
 #ifndef MS_G32
 #define MS_G32 3           // consumer groups, fp32 weights (more registers per thread: 4 rows in flight)
