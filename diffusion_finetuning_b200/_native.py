@@ -42,6 +42,8 @@ SIGNATURES = {
                                    _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_linear_bwd_dx": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _vp, _f32, _vp, _vp, _i64,
                                       _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_linear_bwd_dx_f32out": (_i32, [_vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200lora_linear_bwd_dx_fused_f32out": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_linear_fwd_geglu": (_i32, [_vp, _vp, _vp, _i32, _f32, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_geglu_bwd": (_i32, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "b200lora_lora_grads": (_i32, [_vp, _vp, _vp, _vp, _f32, _vp, _vp, _i64, _i32, _i32, _i32,

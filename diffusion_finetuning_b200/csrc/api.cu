@@ -147,7 +147,7 @@ static void bind_context() {
   }
 }
 
-// 2-D row-major [rows, cols] 16-bit tensor, box [box_rows, box_cols]
+// 2-D row-major [rows, cols] tensor of dtype `dt` (16-bit operands; fp32 for the fp32-output store map), box [box_rows, box_cols]
 static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
                     uint32_t box_rows, uint32_t box_cols, int dt, CUtensorMapSwizzle sw) {
   TmKey key;
@@ -164,11 +164,12 @@ static int get_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t c
   if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return B200LORA_E_CUDA; }
   bind_context();
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 2};
+  cuuint64_t gstr[1] = {ld * (dt == B200LORA_F32 ? 4ull : 2ull)};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUtensorMapDataType cdt =
-      dt == B200LORA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUtensorMapDataType cdt = dt == B200LORA_F32    ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                            : dt == B200LORA_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                  : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   CUresult rc = fn(out, cdt, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -311,9 +312,10 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
                    const void* S1_pack, const void* S2_pack, float scale, void* Y, long long ldy,
                    void* T_out, long long M, int Kc, int Nout, int r, int io_dtype,
                    cudaStream_t stream, const ConvGeoH* cg = nullptr, const XSegs* xs = nullptr,
-                   const GegluH* gg = nullptr) {
+                   const GegluH* gg = nullptr, bool out_f32 = false) {
   TcParams p;
   memset(&p, 0, sizeof(p));
+  p.out_f32 = out_f32 ? 1 : 0;
   if (xs) p.kseg = xs->cols / 64;
   if (gg) { p.geglu = gg->d_ff; p.geglu_store_y = gg->store_y; }
   if (cg) {
@@ -399,8 +401,11 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
   if ((rc = get_tmap(&tmS2, S2_pack, (uint64_t)Nout, 64, 64, (uint32_t)(p.BN / 2), 64, io_dtype,
                      CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   if (gg && !gg->store_y) tmY = tmOut;      // (no pre-activation wanted: the map is never used)
-  else if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
-                          CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  else if (out_f32) {                       // fp32 Y: [32 rows x 16 columns] boxes = the 64-byte staging rows
+    if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 16, B200LORA_F32,
+                       CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+  } else if ((rc = get_tmap(&tmY, Y, (uint64_t)M, (uint64_t)Nout, (uint64_t)ldy, 32, 32, io_dtype,
+                            CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if (!gg) tmOut = tmY;
   cudaError_t e = io_dtype == B200LORA_BF16
                       ? launch_tc2<__nv_bfloat16>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem, stream)
@@ -596,6 +601,24 @@ extern "C" int b200lora_linear_bwd_dx(const void* dY, const void* W, int w_layou
                             s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype, impl, stream);
 }
 
+// Backward dX with an fp32 result (the layer's input was fp32 under autocast: autograd wants an fp32 gradient, and the
+// accumulator is fp32 already — the bf16 -> fp32 cast launch behind the kernel disappears).  tcgen05 pair kernel only.
+extern "C" int b200lora_linear_bwd_dx_f32out(const void* dY, const void* Wt, const void* pack, float scale, float* dX,
+                                             void* dT_out, int64_t M, int K, int N, int r, int io_dtype,
+                                             b200lora_stream_t stream_) {
+  g_err[0] = 0;
+  if (!dY || !Wt || !pack || !dX) { set_error("null pointer argument"); return B200LORA_E_ARG; }
+  if (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16) { set_error("fp32 dX output needs 16-bit io"); return B200LORA_E_DTYPE; }
+  if (M <= 0) return 0;
+  if (!use_pair()) { set_error("fp32 dX output lives in the CTA-pair kernel (B200LORA_PAIR=0 is set)"); return B200LORA_E_ARG; }
+  if (!tc_applicable(dY, N, Wt, N, B200LORA_W_NK, dX, K, r, io_dtype, K) || (N % 8)) return B200LORA_E_ALIGN;
+  const char* pk = reinterpret_cast<const char*>(pack);
+  const void* s1p = pk + 2ll * 16 * K;                                   // Bt_pack [16, N]
+  const void* s2p = pk + 2ll * (16 * ((int64_t)K + N) + 64ll * N);       // At_pack [K, 64]
+  return run_tc2(dY, N, Wt, N, false, s1p, s2p, scale, dX, K, dT_out, M, N, K, r, io_dtype,
+                 reinterpret_cast<cudaStream_t>(stream_), nullptr, nullptr, nullptr, true);
+}
+
 // GEGLU projection with the activation in the epilogue: W0 = [hidden ; gate] rows [2*d_ff, K];
 // out = hidden * gelu(gate) [M, d_ff]; Y [M, 2*d_ff] (the pre-activation, what the backward needs) is optional.
 extern "C" int b200lora_linear_fwd_geglu(const void* X, const void* W0, const void* pack, int has_bias, float scale,
@@ -639,10 +662,9 @@ extern "C" int b200lora_geglu_bwd(const void* dout, const void* Y, void* dY, int
 // operands (W_cat [nseg*Nseg, K], pack of A_cat [r_total, K] and the block-diagonal, scale-folded B);
 // these two entry points are the backward: dY arrives as nseg separate tensors.
 // =========================================================================================
-extern "C" int b200lora_linear_bwd_dx_fused(const void* const* dY, const int64_t* ld_dy, int nseg,
-                                            const void* Wt, const void* pack, void* dX, void* dT_out,
-                                            int64_t M, int K, int Nseg, int r_total, int io_dtype,
-                                            b200lora_stream_t stream_) {
+static int bwd_dx_fused_impl(const void* const* dY, const int64_t* ld_dy, int nseg, const void* Wt, const void* pack,
+                             void* dX, void* dT_out, int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                             b200lora_stream_t stream_, bool out_f32) {
   // dX = sum_i dY_i·W0_i + dT·A_cat with dT = [dY_0 | dY_1 | ..]·B_bd riding as rank rows; Wt is
   // W_catᵀ stored [K, nseg*Nseg] (the W_NK operand of the transposed problem)
   g_err[0] = 0;
@@ -662,8 +684,21 @@ extern "C" int b200lora_linear_bwd_dx_fused(const void* const* dY, const int64_t
   const char* pk = reinterpret_cast<const char*>(pack);
   const void* s1p = pk + 2ll * 16 * K;                                       // Bt_pack [16, Ncat]
   const void* s2p = pk + 2ll * (16 * ((int64_t)K + Ncat) + 64ll * Ncat);     // At_pack [K, 64]
+  if (out_f32 && !use_pair()) { set_error("fp32 dX output lives in the CTA-pair kernel (B200LORA_PAIR=0 is set)"); return B200LORA_E_ARG; }
   return run_tc2(dY[0], ld_dy[0], Wt, Ncat, false, s1p, s2p, 1.0f, dX, K, dT_out, M, Ncat, K, r_total, io_dtype,
-                 reinterpret_cast<cudaStream_t>(stream_), nullptr, &xs);
+                 reinterpret_cast<cudaStream_t>(stream_), nullptr, &xs, nullptr, out_f32);
+}
+extern "C" int b200lora_linear_bwd_dx_fused(const void* const* dY, const int64_t* ld_dy, int nseg,
+                                            const void* Wt, const void* pack, void* dX, void* dT_out,
+                                            int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                                            b200lora_stream_t stream_) {
+  return bwd_dx_fused_impl(dY, ld_dy, nseg, Wt, pack, dX, dT_out, M, K, Nseg, r_total, io_dtype, stream_, false);
+}
+extern "C" int b200lora_linear_bwd_dx_fused_f32out(const void* const* dY, const int64_t* ld_dy, int nseg,
+                                                   const void* Wt, const void* pack, float* dX, void* dT_out,
+                                                   int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                                                   b200lora_stream_t stream_) {
+  return bwd_dx_fused_impl(dY, ld_dy, nseg, Wt, pack, dX, dT_out, M, K, Nseg, r_total, io_dtype, stream_, true);
 }
 
 extern "C" int b200lora_lora_grads_fused(const void* const* dY, const int64_t* ld_dy, int nseg, const void* X,

@@ -57,6 +57,8 @@ struct TcParams {
                               // hidden columns and the BN/2 gate columns of the same outputs, the epilogue also writes
                               // hidden * gelu(gate) [M, geglu] (tmOut); Nout = 2*geglu, num_n_blk counts BN/2-wide blocks
   int geglu_store_y;          // ... and still stores the pre-activation Y [M, 2*geglu] (needed by the backward)
+  int out_f32;                // pair kernel: Y is an fp32 tensor (tmY: 16-column boxes): the accumulator is stored unrounded
+                              // (backward dX of a layer whose input is fp32 under autocast: no bf16 -> fp32 cast launch)
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;
 };

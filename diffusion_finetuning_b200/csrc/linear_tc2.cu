@@ -645,10 +645,32 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           const bool more = ci + 1 < MAX_CI && live(c + 2);
           if (more) tmem_ld_x32(acc_addr + (c + 2) * EPI_COLS, v[(ci + 1) & 1]);
           else release_stage();
+          const uint32_t* w = v[ci & 1];
+          if (p.out_f32) {
+            // fp32 output: the chunk's 32 accumulator columns leave as two [32 rows x 16 columns] boxes (64-byte rows,
+            // the staging buffers' size and swizzle unchanged), unrounded
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              if (lane == 0) tma_store_wait_read<1>();
+              __syncwarp();
+              const uint32_t dst = stg_row + buf * (32 * EPI_COLS * 2);
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                st_shared_v4(dst + ((q ^ wr_sw) << 4), w[hh * 16 + q * 4 + 0], w[hh * 16 + q * 4 + 1],
+                             w[hh * 16 + q * 4 + 2], w[hh * 16 + q * 4 + 3]);
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_2d(&tmY, my_staging + buf * (32 * EPI_COLS * 2), n_blk * BN + c * EPI_COLS + hh * 16,
+                             m_blk * 256 + (int)rank * BM + qd * 32);
+                tma_store_commit();
+              }
+              buf ^= 1;
+            }
+          } else {
           if (lane == 0) tma_store_wait_read<1>();
           __syncwarp();
           const uint32_t dst = stg_row + buf * (32 * EPI_COLS * 2);
-          const uint32_t* w = v[ci & 1];
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             st_shared_v4(dst + ((q ^ wr_sw) << 4),
@@ -664,6 +686,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             tma_store_commit();
           }
           buf ^= 1;
+          }
         }
       }
       if (!released) release_stage();      // a warp with no live chunk in this tile (ragged N) still owes its arrival

@@ -224,15 +224,17 @@ class _FusedSiblingFn(torch.autograd.Function):
         stream = nat.stream_ptr(dev)
         dyp = (ctypes.c_void_p * n)(*[d.data_ptr() for d in d2])
         ldp = (ctypes.c_int64 * n)(*[d.stride(0) for d in d2])
-        dx = torch.empty((M, K), dtype=cdt, device=dev)
+        f32out = need_x and x_dtype == torch.float32 and ops._f32out_enabled()     # see ops._LoraLinearFn.backward
+        dx = torch.empty((M, K), dtype=torch.float32 if f32out else cdt, device=dev)
         dT = torch.empty((M, r_total), dtype=cdt, device=dev)
         grads = [None] * (2 * n)
         if M > 0:
             with torch.cuda.device(dev):
                 wt = group.w_cat(cdt, True)
                 with ops._Prof("bwd_dx", M, K, N * n, r_total, x2.element_size()):
-                    rc = lib.b200lora_linear_bwd_dx_fused(dyp, ldp, n, nat.ptr(wt), nat.ptr(pack), nat.ptr(dx),
-                                                          nat.ptr(dT), M, K, N, r_total, io, stream)
+                    entry = lib.b200lora_linear_bwd_dx_fused_f32out if f32out else lib.b200lora_linear_bwd_dx_fused
+                    rc = entry(dyp, ldp, n, nat.ptr(wt), nat.ptr(pack), nat.ptr(dx), nat.ptr(dT), M, K, N, r_total, io,
+                               stream)
                     nat.check(rc, "b200lora_linear_bwd_dx_fused")
                 if need_ab:
                     use_sink = all(s is not None for s in sinks) and all(ctx.needs_input_grad[2:])

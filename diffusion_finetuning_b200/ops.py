@@ -149,6 +149,11 @@ class _Prof:
         return False
 
 
+def _f32out_enabled():
+    """fp32 dX straight from the pair kernel's epilogue (B200LORA_F32OUT=0 keeps the 16-bit store + ATen cast: A/B)."""
+    return os.environ.get("B200LORA_F32OUT", "1") != "0" and os.environ.get("B200LORA_PAIR", "1") != "0"
+
+
 class GradSink:
     """Where the gradient reductions of one injected layer land: fp32 slices of a flat gradient
     arena (dp.LoraGradArena).  With a sink the dA/dB kernel ADDS straight into the arena (no
@@ -267,13 +272,19 @@ class _LoraLinearFn(torch.autograd.Function):
                 # dX = dY·W0 + s·(dY·B)·A and dT = dY·B in one kernel.  When only dA is needed
                 # (frozen input, e.g. attn2.to_k on the text context) dX is still produced: dT
                 # falls out of the same pass.
-                dx = torch.empty((M, K), dtype=cdt, device=dev)
+                # fp32 input under autocast (LayerNorm outputs are fp32): autograd wants an fp32 dX — the pair kernel
+                # stores its fp32 accumulator directly, no bf16 -> fp32 cast launch behind it
+                f32out = use_tc and need_x and x_dtype == torch.float32 and _f32out_enabled()
+                dx = torch.empty((M, K), dtype=torch.float32 if f32out else cdt, device=dev)
                 dT = torch.empty((M, r), dtype=cdt, device=dev)
                 if use_tc:
                     wt = cache.get(w0, "t", cdt)
                 prof = _Prof("bwd_dx", M, K, N, r, dy2.element_size())
                 prof.__enter__()
-                if use_tc:
+                if f32out:
+                    rc = lib.b200lora_linear_bwd_dx_f32out(nat.ptr(dy2), nat.ptr(wt), nat.ptr(pack), scale, nat.ptr(dx),
+                                                           nat.ptr(dT), M, K, N, r, io_code, stream)
+                elif use_tc:
                     rc = lib.b200lora_linear_bwd_dx(nat.ptr(dy2), nat.ptr(wt), nat.W_NK, nat.ptr(Ac),
                                                     nat.ptr(Bc), ab_code, nat.ptr(pack), scale, nat.ptr(dx),
                                                     nat.ptr(dT), M, K, N, r, io_code, nat.IMPL_TC, stream)

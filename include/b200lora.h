@@ -237,6 +237,20 @@ int b200lora_lora_grads_static(const void* dY, const void* X, const void* T, con
                                b200lora_stream_t stream);
 
 /*
+ * b200lora_linear_bwd_dx / _fused with an FP32 dX: the same kernels, the accumulator stored unrounded.  Replaces the
+ * bf16 -> fp32 cast autograd needs behind the backward of lora.py:50 when the layer's input was fp32 under autocast
+ * (LayerNorm outputs are): one elementwise launch and a [M, K] round trip less per layer.  Wt = W0ᵀ [K, N] (the W_NK
+ * operand of the transposed problem); 16-bit io, tcgen05 CTA-pair kernel only (other cases: the plain entry + a cast).
+ */
+int b200lora_linear_bwd_dx_f32out(const void* dY, const void* Wt, const void* pack, float scale, float* dX,
+                                  void* dT_out, int64_t M, int K, int N, int r, int io_dtype,
+                                  b200lora_stream_t stream);
+int b200lora_linear_bwd_dx_fused_f32out(const void* const* dY, const int64_t* ld_dy, int nseg,
+                                        const void* Wt, const void* pack, float* dX, void* dT_out,
+                                        int64_t M, int K, int Nseg, int r_total, int io_dtype,
+                                        b200lora_stream_t stream);
+
+/*
  * GEGLU projection with the activation in the GEMM epilogue — replaces, for a LoRA-injected
  * `GEGLU.proj` (lora.py:53 lists GEGLU among the default targets), the caller's
  *     hidden, gate = proj(x).chunk(2, dim=-1); out = hidden * gelu(gate)

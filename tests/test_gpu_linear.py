@@ -283,3 +283,37 @@ def test_gradient_reductions_all_modes(shape, dtype):
     assert torch.equal(a0, a1) and torch.equal(b0, b1)          # deterministic mode is bit-reproducible
     dA, dB = run(True, True, False, init=1.0)                   # accumulates, does not overwrite
     assert rel_err(dA - 1.0, dA_ref) < 1e-4 and rel_err(dB - 1.0, dB_ref) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(2048, 320, 320, 4), (777, 640, 1920, 16), (130, 1280, 1280, 8), (4100, 320, 72, 3)])
+def test_backward_dx_fp32_output_equals_the_16bit_store(shape, dtype):
+    """b200lora_linear_bwd_dx_f32out: the same kernel with the fp32 accumulator stored unrounded (what autograd needs when
+    the layer's input was fp32 under autocast).  Rounded to the io dtype it must equal the 16-bit store BIT for bit, and it
+    must agree with the fp32 oracle at least as well; dT is unchanged."""
+    M, K, N, r = shape
+    g = torch.Generator(DEV).manual_seed(21)
+    dy = torch.randn(M, N, device=DEV, generator=g).to(dtype)
+    w0 = (torch.randn(N, K, device=DEV, generator=g) * 0.05).to(dtype)
+    A = (torch.randn(r, K, device=DEV, generator=g) / r).to(dtype)
+    B = (torch.randn(N, r, device=DEV, generator=g) * 0.05).to(dtype)
+    s = 0.7
+    lib, io, st = nat.lib(), nat.dtype_code(dtype), nat.stream_ptr(torch.device(DEV))
+    pack = torch.empty(80 * (K + N), dtype=dtype, device=DEV)
+    nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), io, None, 0, nat.ptr(pack), K, N, r, io, st), "pack")
+    wt = w0.t().contiguous()
+    dx16 = torch.empty(M, K, dtype=dtype, device=DEV)
+    dx32 = torch.full((M, K), float("nan"), dtype=torch.float32, device=DEV)
+    dT16 = torch.empty(M, r, dtype=dtype, device=DEV)
+    dT32 = torch.empty(M, r, dtype=dtype, device=DEV)
+    nat.check(lib.b200lora_linear_bwd_dx(nat.ptr(dy), nat.ptr(wt), nat.W_NK, nat.ptr(A), nat.ptr(B), io, nat.ptr(pack), s,
+                                         nat.ptr(dx16), nat.ptr(dT16), M, K, N, r, io, nat.IMPL_TC, st), "bwd_dx")
+    nat.check(lib.b200lora_linear_bwd_dx_f32out(nat.ptr(dy), nat.ptr(wt), nat.ptr(pack), s, nat.ptr(dx32), nat.ptr(dT32),
+                                                M, K, N, r, io, st), "bwd_dx_f32out")
+    torch.cuda.synchronize()
+    assert torch.isfinite(dx32).all()                      # every element written (ragged M / K tiles included)
+    assert torch.equal(dx32.to(dtype), dx16)
+    assert torch.equal(dT32, dT16)
+    c = lambda t: t.detach().float().cpu()
+    want = c(dy) @ c(w0) + ((c(dy) * s) @ c(B)).to(dtype).float() @ c(A)
+    assert rel_err(dx32, want) < 2e-2 and rel_err(dx32, want) <= rel_err(dx16, want) + 1e-6
