@@ -38,6 +38,8 @@ SIGNATURES = {
     "b200lora_pack_elems": (_i64, [_i32, _i32]),
     "b200lora_pack_lora": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_pack_lora_fused": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp]),
+    "b200lora_pack_lora_cast": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _i64, _vp]),
+    "b200lora_pack_lora_fused_cast": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _i64, _vp]),
     "b200lora_linear_fwd": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp, _f32, _vp, _vp, _i64,
                                    _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200lora_linear_bwd_dx": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _vp, _f32, _vp, _vp, _i64,

@@ -44,9 +44,10 @@ template <typename TIO>
 cudaError_t launch_conv_zcat_tc(const CUtensorMap*, const CUtensorMap*, const void*, int, float, void*, void*,
                                 long long, int, int, int, int, int, cudaStream_t);
 cudaError_t launch_pack(const void*, const void*, int, const void*, int, void*, void*, void*, void*,
-                        int, int, int, int, cudaStream_t);
+                        int, int, int, int, cudaStream_t, const float*, void*, long long);
 cudaError_t launch_pack_seg(const void* const*, const void* const*, const void* const*, const float*, const int*,
-                            int, int, int, void*, void*, void*, void*, int, int, int, cudaStream_t);
+                            int, int, int, void*, void*, void*, void*, int, int, int, cudaStream_t, const float*, void*,
+                            long long);
 template <typename TIO>
 cudaError_t launch_simt(const void*, long long, const void*, long long, int, const void*, int,
                         const void*, long long, long long, const void*, long long, long long, int,
@@ -474,11 +475,19 @@ extern "C" void b200lora_debug_timeline(void* buf, int cta) {
 
 extern "C" int64_t b200lora_pack_elems(int K, int N) { return 80ll * ((int64_t)K + N); }
 
-extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, const void* bias,
-                                  int bias_dtype, void* pack, int K, int N, int r, int io_dtype,
-                                  b200lora_stream_t stream_) {
+static bool cast_args_ok(const float* x_src, const void* x_dst, int64_t x_elems) {
+  if (x_elems == 0) return true;
+  if (x_elems < 0 || !x_src || !x_dst) { set_error("pack + cast: null source / destination"); return false; }
+  if (!aligned16(x_src) || !aligned16(x_dst)) { set_error("pack + cast: source and destination must be 16-byte aligned"); return false; }
+  return true;
+}
+
+static int pack_lora_impl(const void* A, const void* B, int ab_dtype, const void* bias,
+                          int bias_dtype, void* pack, int K, int N, int r, int io_dtype,
+                          b200lora_stream_t stream_, const float* x_src, void* x_dst, int64_t x_elems) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   g_err[0] = 0;
+  if (!cast_args_ok(x_src, x_dst, x_elems)) return B200LORA_E_ARG;
   if (!A || !B || !pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (!valid_dtype(ab_dtype) || (bias && !valid_dtype(bias_dtype)) ||
       (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
@@ -492,16 +501,27 @@ extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, co
   void* Bn_pack = base + 2ll * 16 * (K + N);
   void* At_pack = base + 2ll * (16 * (K + N) + 64ll * N);
   cudaError_t e = launch_pack(A, B, ab_dtype, bias, bias_dtype, A_pack, Bt_pack, Bn_pack, At_pack, K,
-                              N, r, io_dtype, stream);
+                              N, r, io_dtype, stream, x_src, x_dst, x_elems);
   if (e != cudaSuccess) { set_error("pack launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
 }
+extern "C" int b200lora_pack_lora(const void* A, const void* B, int ab_dtype, const void* bias,
+                                  int bias_dtype, void* pack, int K, int N, int r, int io_dtype,
+                                  b200lora_stream_t stream_) {
+  return pack_lora_impl(A, B, ab_dtype, bias, bias_dtype, pack, K, N, r, io_dtype, stream_, nullptr, nullptr, 0);
+}
+extern "C" int b200lora_pack_lora_cast(const void* A, const void* B, int ab_dtype, const void* bias,
+                                       int bias_dtype, void* pack, int K, int N, int r, int io_dtype,
+                                       const float* x_src, void* x_dst, int64_t x_elems, b200lora_stream_t stream_) {
+  return pack_lora_impl(A, B, ab_dtype, bias, bias_dtype, pack, K, N, r, io_dtype, stream_, x_src, x_dst, x_elems);
+}
 
-extern "C" int b200lora_pack_lora_fused(const void* const* A, const void* const* B, const void* const* bias,
-                                        const float* scales, const int* r_each, int nseg, int ab_dtype,
-                                        int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
-                                        b200lora_stream_t stream_) {
+static int pack_lora_fused_impl(const void* const* A, const void* const* B, const void* const* bias,
+                                const float* scales, const int* r_each, int nseg, int ab_dtype,
+                                int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                                b200lora_stream_t stream_, const float* x_src, void* x_dst, int64_t x_elems) {
   g_err[0] = 0;
+  if (!cast_args_ok(x_src, x_dst, x_elems)) return B200LORA_E_ARG;
   if (!A || !B || !scales || !r_each || !pack) { set_error("null pointer argument"); return B200LORA_E_ARG; }
   if (nseg < 1 || nseg > 4) { set_error("pack_lora_fused: 1 <= nseg <= 4"); return B200LORA_E_SHAPE; }
   if (!valid_dtype(ab_dtype) || (io_dtype != B200LORA_BF16 && io_dtype != B200LORA_F16)) {
@@ -524,9 +544,24 @@ extern "C" int b200lora_pack_lora_fused(const void* const* A, const void* const*
   cudaError_t e = launch_pack_seg(A, B, bias, scales, r_each, nseg, ab_dtype, bias_dtype, base,
                                   base + 2ll * 16 * K, base + 2ll * 16 * (K + N),
                                   base + 2ll * (16 * (K + N) + 64ll * N), K, Nseg, io_dtype,
-                                  reinterpret_cast<cudaStream_t>(stream_));
+                                  reinterpret_cast<cudaStream_t>(stream_), x_src, x_dst, x_elems);
   if (e != cudaSuccess) { set_error("pack_lora_fused launch failed: %s", cudaGetErrorString(e)); return B200LORA_E_CUDA; }
   return 0;
+}
+extern "C" int b200lora_pack_lora_fused(const void* const* A, const void* const* B, const void* const* bias,
+                                        const float* scales, const int* r_each, int nseg, int ab_dtype,
+                                        int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                                        b200lora_stream_t stream_) {
+  return pack_lora_fused_impl(A, B, bias, scales, r_each, nseg, ab_dtype, bias_dtype, pack, K, Nseg, io_dtype, stream_,
+                              nullptr, nullptr, 0);
+}
+extern "C" int b200lora_pack_lora_fused_cast(const void* const* A, const void* const* B, const void* const* bias,
+                                             const float* scales, const int* r_each, int nseg, int ab_dtype,
+                                             int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                                             const float* x_src, void* x_dst, int64_t x_elems,
+                                             b200lora_stream_t stream_) {
+  return pack_lora_fused_impl(A, B, bias, scales, r_each, nseg, ab_dtype, bias_dtype, pack, K, Nseg, io_dtype, stream_,
+                              x_src, x_dst, x_elems);
 }
 
 extern "C" int b200lora_lora_gemm(const void* X, int64_t ldx, const void* W, int64_t ldw,

@@ -232,12 +232,31 @@ cudaError_t launch_svd_epilogue(float* U, const float* S, float* Vh, float hi, i
 //   Bn_pack [N, 64]  = B  rows, column r = bias[n] (if any), rest zero  forward  tail block (S2)
 //   At_pack [K, 64]  = Aᵀ rows, columns r..63 zero                      backward tail block (S2)
 // One launch per (A, B) version; O(80·(K+N)) elements.
+// fp32 -> TIO conversion of the layer's input riding in the pack launch (training under autocast: the input of a layer
+// behind a LayerNorm is fp32; one launch instead of an ATen cast + the pack, and the consuming GEMM's prologue overlaps
+// this grid through the programmatic launch).  8 elements per thread and pass: two 16-byte loads, one 16-byte store.
+template <typename TIO>
+__device__ __forceinline__ void cast_rows(const float* __restrict__ src, TIO* __restrict__ dst, long long n) {
+  const long long nv = n >> 3;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    const float4 a = __ldcs(reinterpret_cast<const float4*>(src) + 2 * i);
+    const float4 b = __ldcs(reinterpret_cast<const float4*>(src) + 2 * i + 1);
+    TIO o[8];
+    o[0] = from_f32<TIO>(a.x); o[1] = from_f32<TIO>(a.y); o[2] = from_f32<TIO>(a.z); o[3] = from_f32<TIO>(a.w);
+    o[4] = from_f32<TIO>(b.x); o[5] = from_f32<TIO>(b.y); o[6] = from_f32<TIO>(b.z); o[7] = from_f32<TIO>(b.w);
+    *(reinterpret_cast<uint4*>(dst) + i) = *reinterpret_cast<const uint4*>(o);
+  }
+  for (long long i = (nv << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = from_f32<TIO>(src[i]);
+}
+
 template <typename TIO>
 __global__ void lora_pack_kernel(const void* __restrict__ A, const void* __restrict__ B, int ab_dtype,
                                  const void* __restrict__ bias, int bias_dtype,
                                  TIO* __restrict__ A_pack, TIO* __restrict__ Bt_pack,
                                  TIO* __restrict__ Bn_pack, TIO* __restrict__ At_pack, int K, int N,
-                                 int r) {
+                                 int r, const float* __restrict__ xsrc, TIO* __restrict__ xdst, long long xn) {
   const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
   // the GEMM that consumes this pack is the next launch on the stream: let its prologue (TMEM allocation,
   // barrier init, descriptor prefetch) run under this grid; its griddepcontrol.wait still sees a finished pack
@@ -263,22 +282,25 @@ __global__ void lora_pack_kernel(const void* __restrict__ A, const void* __restr
       At_pack[t] = from_f32<TIO>(j < r ? load_as_float(A, ab_dtype, (long long)j * K + k) : 0.f);
     }
   }
+  if (xn > 0) cast_rows<TIO>(xsrc, xdst, xn);
 }
 
 cudaError_t launch_pack(const void* A, const void* B, int ab_dtype, const void* bias, int bias_dtype,
                         void* A_pack, void* Bt_pack, void* Bn_pack, void* At_pack, int K, int N,
-                        int r, int io_dtype, cudaStream_t stream) {
+                        int r, int io_dtype, cudaStream_t stream, const float* xsrc, void* xdst, long long xn) {
   const int total = 80 * (K + N);
-  int blocks = (total + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  long long work = total;
+  if (xn / 8 > work) work = xn / 8;
+  int blocks = (int)((work + 255) / 256 < 148 * 8 ? (work + 255) / 256 : 148 * 8);
+  if (blocks < 1) blocks = 1;
   if (io_dtype == B200LORA_BF16)
     lora_pack_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
         A, B, ab_dtype, bias, bias_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack,
-        (__nv_bfloat16*)Bn_pack, (__nv_bfloat16*)At_pack, K, N, r);
+        (__nv_bfloat16*)Bn_pack, (__nv_bfloat16*)At_pack, K, N, r, xsrc, (__nv_bfloat16*)xdst, xn);
   else
     lora_pack_kernel<__half><<<blocks, 256, 0, stream>>>(
         A, B, ab_dtype, bias, bias_dtype, (__half*)A_pack, (__half*)Bt_pack, (__half*)Bn_pack,
-        (__half*)At_pack, K, N, r);
+        (__half*)At_pack, K, N, r, xsrc, (__half*)xdst, xn);
   return cudaGetLastError();
 }
 
@@ -298,7 +320,8 @@ struct PackSegs {
 template <typename TIO>
 __global__ void lora_pack_seg_kernel(const PackSegs sg, int ab_dtype, int bias_dtype, TIO* __restrict__ A_pack,
                                      TIO* __restrict__ Bt_pack, TIO* __restrict__ Bn_pack,
-                                     TIO* __restrict__ At_pack, int K, int Nseg, int r_total) {
+                                     TIO* __restrict__ At_pack, int K, int Nseg, int r_total,
+                                     const float* __restrict__ xsrc, TIO* __restrict__ xdst, long long xn) {
   const int N = sg.nseg * Nseg;
   const int n0 = 16 * K, n1 = n0 + 16 * N, n2 = n1 + 64 * N, total = n2 + 64 * K;
   pdl_launch_dependents();      // as in lora_pack_kernel
@@ -344,12 +367,13 @@ __global__ void lora_pack_seg_kernel(const PackSegs sg, int ab_dtype, int bias_d
       At_pack[t] = from_f32<TIO>(a_val(j, k));
     }
   }
+  if (xn > 0) cast_rows<TIO>(xsrc, xdst, xn);
 }
 
 cudaError_t launch_pack_seg(const void* const* A, const void* const* B, const void* const* bias,
                             const float* scales, const int* r_each, int nseg, int ab_dtype, int bias_dtype,
                             void* A_pack, void* Bt_pack, void* Bn_pack, void* At_pack, int K, int Nseg,
-                            int io_dtype, cudaStream_t stream) {
+                            int io_dtype, cudaStream_t stream, const float* xsrc, void* xdst, long long xn) {
   PackSegs sg = {};
   sg.nseg = nseg;
   int off = 0;
@@ -363,16 +387,18 @@ cudaError_t launch_pack_seg(const void* const* A, const void* const* B, const vo
     off += r_each[s];
   }
   const int total = 80 * (K + nseg * Nseg);
-  int blocks = (total + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  long long work = total;
+  if (xn / 8 > work) work = xn / 8;
+  int blocks = (int)((work + 255) / 256 < 148 * 8 ? (work + 255) / 256 : 148 * 8);
+  if (blocks < 1) blocks = 1;
   if (io_dtype == B200LORA_BF16)
     lora_pack_seg_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
         sg, ab_dtype, bias_dtype, (__nv_bfloat16*)A_pack, (__nv_bfloat16*)Bt_pack, (__nv_bfloat16*)Bn_pack,
-        (__nv_bfloat16*)At_pack, K, Nseg, off);
+        (__nv_bfloat16*)At_pack, K, Nseg, off, xsrc, (__nv_bfloat16*)xdst, xn);
   else
     lora_pack_seg_kernel<__half><<<blocks, 256, 0, stream>>>(
         sg, ab_dtype, bias_dtype, (__half*)A_pack, (__half*)Bt_pack, (__half*)Bn_pack, (__half*)At_pack, K,
-        Nseg, off);
+        Nseg, off, xsrc, (__half*)xdst, xn);
   return cudaGetLastError();
 }
 

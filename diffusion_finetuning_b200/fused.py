@@ -94,8 +94,9 @@ class SiblingGroup:
         self._store[slot] = (key, out)
         return out
 
-    def pack(self, cdt, live=False):
-        """(pack buffer, a bias tensor or None — only its presence matters to the GEMM call)."""
+    def pack(self, cdt, live=False, cast=None):
+        """(pack buffer, a bias tensor or None — only its presence matters to the GEMM call).  `cast` = (fp32 input,
+        destination in `cdt`): the input's conversion rides in the pack launch (ops.BaseWeightCache.lora_pack)."""
         Ls = self.layers
         key = tuple((_key(m.lora_down.weight), _key(m.lora_up.weight), float(m.scale),
                      None if m.linear.bias is None else _key(m.linear.bias)) for m in Ls) + (cdt,)
@@ -117,12 +118,16 @@ class SiblingGroup:
         buf = torch.empty(80 * (K + N * n), dtype=cdt, device=dev)
         vp = ctypes.c_void_p
         with torch.cuda.device(dev):
-            rc = nat.lib().b200lora_pack_lora_fused(
-                (vp * n)(*[t.data_ptr() for t in As]), (vp * n)(*[t.data_ptr() for t in Bs]),
-                (vp * n)(*[None if t is None else t.data_ptr() for t in bs]),
-                (ctypes.c_float * n)(*[float(m.scale) for m in Ls]), (ctypes.c_int * n)(*rs), n,
-                nat.dtype_code(As[0].dtype), nat.dtype_code(bias_any.dtype) if bias_any is not None else 0,
-                nat.ptr(buf), K, N, nat.dtype_code(cdt), nat.stream_ptr(dev))
+            head = ((vp * n)(*[t.data_ptr() for t in As]), (vp * n)(*[t.data_ptr() for t in Bs]),
+                    (vp * n)(*[None if t is None else t.data_ptr() for t in bs]),
+                    (ctypes.c_float * n)(*[float(m.scale) for m in Ls]), (ctypes.c_int * n)(*rs), n,
+                    nat.dtype_code(As[0].dtype), nat.dtype_code(bias_any.dtype) if bias_any is not None else 0,
+                    nat.ptr(buf), K, N, nat.dtype_code(cdt))
+            if cast is not None:
+                rc = nat.lib().b200lora_pack_lora_fused_cast(*head, nat.ptr(cast[0]), nat.ptr(cast[1]), cast[0].numel(),
+                                                             nat.stream_ptr(dev))
+            else:
+                rc = nat.lib().b200lora_pack_lora_fused(*head, nat.stream_ptr(dev))
         nat.check(rc, "b200lora_pack_lora(fused)")
         out = (buf, bias_any)
         if not live:
@@ -184,13 +189,20 @@ class _FusedSiblingFn(torch.autograd.Function):
         cdt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
         lead = x.shape[:-1]
         x2 = x.reshape(-1, K)
-        if x2.dtype != cdt:
-            x2 = x2.to(cdt)
-        x2 = x2.contiguous()
         M = x2.shape[0]
         need_grad = group.grad_on and any(ctx.needs_input_grad)
+        live = group.grad_on and any(ctx.needs_input_grad[2:])
+        # fp32 input while the factors are trained: its conversion rides in the pack launch (see ops._LoraLinearFn)
+        ride = x2.dtype == torch.float32 and live and M > 0 and x2.is_contiguous() and ops._castride_enabled()
+        x_f32 = x2 if ride else None
+        if ride:
+            x2 = torch.empty((M, K), dtype=cdt, device=x.device)
+        else:
+            if x2.dtype != cdt:
+                x2 = x2.to(cdt)
+            x2 = x2.contiguous()
         w = group.w_cat(cdt, False)
-        pack, bias_flag = group.pack(cdt, live=group.grad_on and any(ctx.needs_input_grad[2:]))
+        pack, bias_flag = group.pack(cdt, live=live, cast=(x_f32, x2) if ride else None)
         y = torch.empty((M, Ncat), dtype=cdt, device=x.device)
         T = torch.empty((M, r_total), dtype=cdt, device=x.device) if need_grad else None
         if M > 0:

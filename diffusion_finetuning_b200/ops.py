@@ -53,7 +53,7 @@ class BaseWeightCache:
         self._store[slot] = (key, out)
         return out
 
-    def lora_pack(self, A, B, bias, dtype, live=False):
+    def lora_pack(self, A, B, bias, dtype, live=False, cast=None):
         """The packed LoRA operands of the tcgen05 kernel (b200lora_pack_lora): one buffer of
         80·(K+N) elements in `dtype` holding the rank rows and tail blocks of forward and backward
         (and the frozen bias, which the forward adds through the tail MMA).
@@ -76,10 +76,16 @@ class BaseWeightCache:
         Ac, Bc = A.detach().contiguous(), B.detach().contiguous()
         bc = None if bias is None else bias.detach().contiguous()
         with torch.cuda.device(A.device):
-            rc = nat.lib().b200lora_pack_lora(nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype),
-                                              nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
-                                              nat.ptr(buf), K, N, r, nat.dtype_code(dtype),
-                                              nat.stream_ptr(A.device))
+            if cast is not None:          # (x fp32 contiguous, x_out in `dtype`): the input's conversion rides in this launch
+                rc = nat.lib().b200lora_pack_lora_cast(nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype),
+                                                       nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
+                                                       nat.ptr(buf), K, N, r, nat.dtype_code(dtype), nat.ptr(cast[0]),
+                                                       nat.ptr(cast[1]), cast[0].numel(), nat.stream_ptr(A.device))
+            else:
+                rc = nat.lib().b200lora_pack_lora(nat.ptr(Ac), nat.ptr(Bc), nat.dtype_code(Ac.dtype),
+                                                  nat.ptr(bc), nat.dtype_code(bc.dtype) if bc is not None else 0,
+                                                  nat.ptr(buf), K, N, r, nat.dtype_code(dtype),
+                                                  nat.stream_ptr(A.device))
         nat.check(rc, "b200lora_pack_lora")
         if not live:
             self._store["pack"] = (key, buf)
@@ -149,6 +155,11 @@ class _Prof:
         return False
 
 
+def _castride_enabled():
+    """fp32 -> 16-bit input conversion inside the pack launch (B200LORA_CASTRIDE=0 keeps the ATen cast: A/B)."""
+    return os.environ.get("B200LORA_CASTRIDE", "1") != "0"
+
+
 def _f32out_enabled():
     """fp32 dX straight from the pair kernel's epilogue (B200LORA_F32OUT=0 keeps the 16-bit store + ATen cast: A/B)."""
     return os.environ.get("B200LORA_F32OUT", "1") != "0" and os.environ.get("B200LORA_PAIR", "1") != "0"
@@ -196,10 +207,19 @@ class _LoraLinearFn(torch.autograd.Function):
                 "on the CUDA-core path); the module can still be built, saved, loaded and merged at any rank")
         lead = x.shape[:-1]
         x2 = x.reshape(-1, K)
-        if x2.dtype != cdt:
-            x2 = x2.to(cdt)
-        x2 = x2.contiguous()
         M = x2.shape[0]
+        # fp32 input of a layer whose factors are trained on the tcgen05 path: its conversion rides in the pack launch
+        # (rebuilt on every call anyway) instead of an ATen cast in front of it
+        ride = (x2.dtype == torch.float32 and cdt != torch.float32 and M > 0 and grad_on
+                and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]) and x2.is_contiguous()
+                and _tc_ok(cdt, K, N, r, x.device, impl) and _castride_enabled())
+        x_f32 = x2 if ride else None
+        if ride:
+            x2 = torch.empty((M, K), dtype=cdt, device=x.device)
+        else:
+            if x2.dtype != cdt:
+                x2 = x2.to(cdt)
+            x2 = x2.contiguous()
         if cache is None:
             cache = BaseWeightCache()
         w = w0.detach() if (w0.dtype == cdt and w0.is_contiguous()) else cache.get(w0, "cast", cdt)
@@ -215,7 +235,8 @@ class _LoraLinearFn(torch.autograd.Function):
         T = torch.empty((M, r), dtype=cdt, device=x.device) if need_grad else None
         pack = None
         if use_tc and M > 0:
-            pack = cache.lora_pack(A, B, bias, cdt, live=grad_on and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]))
+            pack = cache.lora_pack(A, B, bias, cdt, live=grad_on and (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]),
+                                   cast=(x_f32, x2) if ride else None)
         out = None
         if geglu:
             if not use_tc:

@@ -135,6 +135,21 @@ int b200lora_pack_lora_fused(const void* const* A, const void* const* B, const v
                              b200lora_stream_t stream);
 
 /*
+ * The two pack launches with the fp32 -> io_dtype conversion of the layer's INPUT riding along: x_dst[i] = rnd(x_src[i])
+ * for x_elems elements (both 16-byte aligned) in the same launch.  Replaces the input cast autocast performs in front
+ * of lora.py:49 (`F.linear` under autocast casts its fp32 input) when the factors are trained and the pack is rebuilt
+ * on every call anyway: one launch instead of two, and the consuming GEMM's prologue overlaps it (programmatic launch).
+ */
+int b200lora_pack_lora_cast(const void* A, const void* B, int ab_dtype,
+                            const void* bias, int bias_dtype, void* pack,
+                            int K, int N, int r, int io_dtype,
+                            const float* x_src, void* x_dst, int64_t x_elems, b200lora_stream_t stream);
+int b200lora_pack_lora_fused_cast(const void* const* A, const void* const* B, const void* const* bias,
+                                  const float* scales, const int* r_each, int nseg, int ab_dtype,
+                                  int bias_dtype, void* pack, int K, int Nseg, int io_dtype,
+                                  const float* x_src, void* x_dst, int64_t x_elems, b200lora_stream_t stream);
+
+/*
  * Forward of LoraInjectedLinear — replaces lora.py:49-50
  *   `self.linear(input) + self.lora_up(self.lora_down(input)) * self.scale`
  * (3 F.linear + mul + add in the reference; one kernel here).

@@ -317,3 +317,60 @@ def test_backward_dx_fp32_output_equals_the_16bit_store(shape, dtype):
     c = lambda t: t.detach().float().cpu()
     want = c(dy) @ c(w0) + ((c(dy) * s) @ c(B)).to(dtype).float() @ c(A)
     assert rel_err(dx32, want) < 2e-2 and rel_err(dx32, want) <= rel_err(dx16, want) + 1e-6
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_pack_with_input_cast_rider(dtype):
+    """b200lora_pack_lora_cast / _fused_cast: the same pack as the plain entries, bit for bit, plus x_dst = x_src rounded to
+    the io dtype (what `x.to(dtype)` gives), for sizes with and without a tail of fewer than 8 elements."""
+    g = torch.Generator(DEV).manual_seed(4)
+    lib, io, st = nat.lib(), nat.dtype_code(dtype), nat.stream_ptr(torch.device(DEV))
+    K, N, r = 320, 640, 4
+    A = torch.randn(r, K, device=DEV, generator=g) / r
+    B = torch.randn(N, r, device=DEV, generator=g) * 0.05
+    bias = torch.randn(N, device=DEV, generator=g)
+    f32 = nat.dtype_code(torch.float32)
+    for n_x in (8192 * 320, 777 * 72 + 5, 8):
+        x = torch.randn(n_x, device=DEV, generator=g) * 3
+        p0 = torch.empty(80 * (K + N), dtype=dtype, device=DEV)
+        p1 = torch.full_like(p0, float("nan"))
+        xd = torch.full((n_x,), float("nan"), dtype=dtype, device=DEV)
+        nat.check(lib.b200lora_pack_lora(nat.ptr(A), nat.ptr(B), f32, nat.ptr(bias), f32, nat.ptr(p0), K, N, r, io, st), "pack")
+        nat.check(lib.b200lora_pack_lora_cast(nat.ptr(A), nat.ptr(B), f32, nat.ptr(bias), f32, nat.ptr(p1), K, N, r, io,
+                                              nat.ptr(x), nat.ptr(xd), n_x, st), "pack_cast")
+        torch.cuda.synchronize()
+        assert torch.equal(p0, p1) and torch.equal(xd, x.to(dtype))
+
+
+def test_training_forward_with_fp32_input_uses_the_cast_rider_and_matches():
+    """Under autocast with an fp32 input and trained factors the layer issues pack(+cast) + GEMM (2 launches, no ATen cast);
+    outputs and gradients equal the B200LORA_CASTRIDE=0 path bit for bit (same conversion, same kernels)."""
+    import os
+    torch.manual_seed(0)
+    m = L.LoraInjectedLinear(320, 640, bias=True, r=4).to(DEV)
+    m.linear.requires_grad_(False)
+    with torch.no_grad():
+        m.lora_up.weight.normal_(0, 0.05)
+    x = torch.randn(4, 500, 320, device=DEV, requires_grad=True)
+    dy = torch.randn(4, 500, 640, device=DEV)
+    res = []
+    for flag in ("1", "0"):
+        os.environ["B200LORA_CASTRIDE"] = flag
+        try:
+            x.grad = None
+            m.lora_down.weight.grad = m.lora_up.weight.grad = None
+            os.environ["B200LORA_DETERMINISTIC"] = "1"
+            n0 = nat.LAUNCHES
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                y = m(x)
+            fwd_launches = nat.LAUNCHES - n0
+            y.backward(dy.to(y.dtype))
+            res.append((y.detach().clone(), x.grad.clone(), m.lora_down.weight.grad.clone(), m.lora_up.weight.grad.clone(),
+                        fwd_launches))
+        finally:
+            os.environ.pop("B200LORA_CASTRIDE", None)
+            os.environ.pop("B200LORA_DETERMINISTIC", None)
+    assert res[0][4] == 2 and res[1][4] == 2          # pack + GEMM either way; the ATen cast is not a C-ABI launch
+    for a, b in zip(res[0][:4], res[1][:4]):
+        assert torch.equal(a, b)
+    assert res[0][1].dtype == torch.float32
