@@ -82,7 +82,10 @@ struct Sched2 {
       p.dbg[(role) * 256 + (it_) * 8 + (k)] = clock64();                              \
   } while (0)
 
-template <typename TIO, bool DBG>
+// MODE: 0 = plain (Y in the io dtype), 1 = GEGLU projection (hidden * gelu(gate) in the epilogue), 2 = fp32 Y.
+// Compile-time, not a TcParams flag: as run-time branches the two extra epilogues cost the PLAIN launches of the training
+// step ~0.5 us each (register ceiling, longer instruction stream).
+template <typename TIO, bool DBG, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(tc2::NUM_THREADS, 1)
 lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmX1,
                      const __grid_constant__ CUtensorMap tmX2, const __grid_constant__ CUtensorMap tmWa,
@@ -90,6 +93,8 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                      const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmY,
                      const __grid_constant__ CUtensorMap tmOut, const TcParams p) {
   using namespace tc2;
+  constexpr bool GEGLU = MODE == 1;
+  constexpr bool F32OUT = MODE == 2;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -142,7 +147,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
     tma_prefetch_desc(&tmS1);
     tma_prefetch_desc(&tmS2);
     tma_prefetch_desc(&tmY);
-    if (p.geglu) {
+    if (GEGLU) {
       tma_prefetch_desc(&tmX1);      // GEGLU mode: W with a [BN/2 x 64] box (hidden rows)
       tma_prefetch_desc(&tmX2);      //             W with an [8 x 64] box (first gate rows of the leader's half)
       tma_prefetch_desc(&tmOut);
@@ -247,7 +252,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
                 tma_load_2d_2sm(a_dst, &tmX, full0, kb * BK, m_blk * 256 + (int)rank * BM, pol_x);
               else     // X split along K into equal segments, one tensor each (fused sibling backward)
                 tma_load_2d_2sm(a_dst, xm, full0, sk * BK, m_blk * 256 + (int)rank * BM, pol_x);
-            } else if (p.geglu) {
+            } else if (GEGLU) {
               // GEGLU projection: B rows of the pair = [hidden j0 .. j0+BN/2) ; gate j0 .. j0+BN/2) ; 16 rank rows].
               // The leader's half (H = BN/2 + 8 rows) is the hidden rows plus the first 8 gate rows (two boxes), the
               // peer's the other BN/2 - 8 gate rows (= H - 16: the usual box) and the rank rows.
@@ -282,7 +287,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             if (leader) mbar_arrive_expect_tx(&full_bar[s], tail_tx);
             else mbar_arrive_cluster(full0);
           } else {
-            const int s2_row = p.geglu ? n_blk * (BN / 2) + (int)rank * p.geglu      // leader: hidden rows, peer: gate rows
+            const int s2_row = GEGLU ? n_blk * (BN / 2) + (int)rank * p.geglu      // leader: hidden rows, peer: gate rows
                                        : n_blk * BN + (int)rank * (BN / 2);
             tma_load_2d_2sm(b_dst, &tmS2, full0, 0, s2_row, pol_w);
           }
@@ -586,7 +591,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         }
         released = true;
       };
-      if (p.geglu) {
+      if (GEGLU) {
         // ---- GEGLU projection: accumulator columns [0, BN/2) = hidden, [BN/2, BN) = gate of the same BN/2 outputs.
         // This warp takes the 32-column chunk pairs pi = half, half + 2, ...: out = hidden * gelu(gate), rounded as the
         // reference composition rounds (projection output, gelu, product: each a tensor of the io dtype), stored
@@ -646,7 +651,7 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           if (more) tmem_ld_x32(acc_addr + (c + 2) * EPI_COLS, v[(ci + 1) & 1]);
           else release_stage();
           const uint32_t* w = v[ci & 1];
-          if (p.out_f32) {
+          if (F32OUT) {
             // fp32 output: the chunk's 32 accumulator columns leave as two [32 rows x 16 columns] boxes (64-byte rows,
             // the staging buffers' size and swizzle unchanged), unrounded
 #pragma unroll
@@ -726,13 +731,13 @@ bool pdl_enabled() {
   return v == 1;
 }
 
-template <typename TIO, bool DBG>
+template <typename TIO, bool DBG, int MODE>
 static cudaError_t launch_tc2_impl(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CUtensorMap& tmX2,
                                    const CUtensorMap& tmWa,
                                    const CUtensorMap& tmWb, const CUtensorMap& tmS1,
                                    const CUtensorMap& tmS2, const CUtensorMap& tmY, const CUtensorMap& tmOut,
                                    const TcParams& p, int smem_bytes, cudaStream_t stream) {
-  auto kern = lora_gemm_tc2_kernel<TIO, DBG>;
+  auto kern = lora_gemm_tc2_kernel<TIO, DBG, MODE>;
   // The opt-in smem cap is a process-wide attribute of the function: raise it ONCE to the device
   // maximum (autograd runs the backward on another thread — a per-thread cache of "what I last
   // set" let one thread lower the cap under the other).  Co-resident pair count is cached per smem.
@@ -786,9 +791,13 @@ cudaError_t launch_tc2(const CUtensorMap& tmX, const CUtensorMap& tmX1, const CU
                        const CUtensorMap& tmWa, const CUtensorMap& tmWb, const CUtensorMap& tmS1,
                        const CUtensorMap& tmS2, const CUtensorMap& tmY, const CUtensorMap& tmOut, const TcParams& p,
                        int smem_bytes, cudaStream_t stream) {
-  if (p.dbg != nullptr)
-    return launch_tc2_impl<TIO, true>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
-  return launch_tc2_impl<TIO, false>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
+  if (p.geglu)
+    return launch_tc2_impl<TIO, false, 1>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
+  if (p.out_f32)
+    return launch_tc2_impl<TIO, false, 2>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
+  if (p.dbg != nullptr)      // (the clock64 timeline exists for the plain kernel only)
+    return launch_tc2_impl<TIO, true, 0>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
+  return launch_tc2_impl<TIO, false, 0>(tmX, tmX1, tmX2, tmWa, tmWb, tmS1, tmS2, tmY, tmOut, p, smem_bytes, stream);
 }
 
 template cudaError_t launch_tc2<__nv_bfloat16>(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&,
