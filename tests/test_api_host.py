@@ -209,3 +209,28 @@ def test_against_reference_directly(reference_lora, tmp_path):
     L.monkeypatch_or_replace_lora(b, torch.load(tmp_path / "a.pt"), r=4)
     R.tune_lora_scale(b, 0.25)       # class-name matching must find OUR class
     assert all(m.scale == 0.25 for m in b.modules() if isinstance(m, L.LoraInjectedLinear))
+
+
+def test_fuse_geglu_patches_and_restores_only_injected_geglu_modules():
+    """`fuse_geglu` routes a `GEGLU` module's forward through its LoRA-injected `proj`; modules whose `proj`
+    is not injected are left alone, patching twice is idempotent, `unfuse_geglu` restores the module's own forward."""
+    import diffusion_finetuning_b200 as L
+    from diffusion_finetuning_b200.unet_sd15 import GEGLU
+
+    class Block(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = GEGLU(64, 128)
+            self.b = GEGLU(64, 128)
+
+    blk = Block()
+    L.inject_trainable_lora(blk.a, {"GEGLU"}, r=4)          # only `a` gets a LoRA projection
+    assert isinstance(blk.a.proj, L.LoraInjectedLinear) and not isinstance(blk.b.proj, L.LoraInjectedLinear)
+    fwd_a, fwd_b = blk.a.forward, blk.b.forward
+    patched = L.fuse_geglu(blk)
+    assert patched == [blk.a] and blk.a.forward is not fwd_a and blk.b.forward == fwd_b
+    assert L.fuse_geglu(blk) == [blk.a]                      # idempotent
+    L.unfuse_geglu(blk)
+    assert blk.a.forward == fwd_a
+    # the un-injected module still runs on the CPU as plain PyTorch
+    assert blk.b(torch.randn(3, 64)).shape == (3, 128)
