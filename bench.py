@@ -166,6 +166,17 @@ class LaunchProfiler:
             return 2.0 * M * K * N + 2.0 * M * r * (K + N), e * (M * N + N * K + M * K + r * (K + N) + M * r)
         if kind == "grads":    # dA, dB token reductions: re-read X and dY once
             return 2.0 * M * r * (K + N), e * (M * K + M * N + 2 * M * r) + 4 * r * (K + N)
+        if kind.startswith("conv_"):
+            # implicit-GEMM LoRA conv (conv_ops._gemm): M output pixels, K = taps * C_in, N = C_out; the input
+            # image is read ONCE (M * K / taps elements at stride 1), not once per tap.  Forward: base conv +
+            # down conv (r more output columns) + up (K=r tail); backward dX: base + the r extra K rows per tap.
+            taps = int(kind.split(":")[1])
+            cin = K // taps
+            if kind.startswith("conv_fwd"):
+                return (2.0 * M * K * N + 2.0 * M * r * (K + N),
+                        e * (M * cin + N * K + M * N + r * (K + N) + M * r))
+            return (2.0 * M * K * N + 2.0 * M * r * taps * N,
+                    e * (M * cin + N * K + M * N + r * taps * N + M * r))
         return 0.0, 0.0
 
     def summary(self):
@@ -1105,12 +1116,18 @@ def main():
     pk = peaks()
     summ = prof.summary()
     gemm = {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0}
-    for k in ("fwd", "bwd_dx"):
-        for f in gemm:
-            gemm[f] += summ.get(k, {}).get(f, 0)
+    conv = {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0}
+    for k, v in summ.items():
+        if k in ("fwd", "bwd_dx") or k.startswith("conv_"):
+            for f in gemm:
+                gemm[f] += v.get(f, 0)
+                if k.startswith("conv_"):
+                    conv[f] += v.get(f, 0)
     step_ms = t_prof / args.steps * 1e3      # shares below are of the profiled steps
     ach_tf = gemm["flops"] / (gemm["ms"] * 1e-3) / 1e12 if gemm["ms"] else 0.0
-    roofline = {"kernel": "lora_gemm_tc2_kernel (fused LoRA linear forward + backward-dX launches, CTA-pair tcgen05)",
+    roofline = {"kernel": "lora_gemm_tc2_kernel (fused LoRA linear forward + backward-dX launches"
+                          + (", and the implicit-GEMM conv launches of the same kernel" if conv["launches"] else "")
+                          + ", CTA-pair tcgen05)",
                 "bound": "tensor", "achieved": ach_tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
                 "frac": ach_tf / pk["tf_sustained"], "peak_source": pk["src"] + " (sustained bf16)",
                 "traffic": None,
@@ -1119,6 +1136,20 @@ def main():
                 "share_of_step": gemm["ms"] / args.steps / step_ms,
                 "profiled_ms_per_step": step_ms, "launch_timing": timing_mode,
                 "achieved_hbm_gbs": gemm["bytes"] / (gemm["ms"] * 1e-3) / 1e9 if gemm["ms"] else 0.0}
+    if conv["launches"]:
+        # the same kernel on its implicit-GEMM (TMA im2col) geometry: the resnet convs of the extended injection
+        roofline["conv_launches"] = {"launches_per_step": conv["launches"] / args.steps,
+                                     "avg_launch_us": conv["ms"] * 1e3 / conv["launches"],
+                                     "achieved": conv["flops"] / (conv["ms"] * 1e-3) / 1e12,
+                                     "frac": conv["flops"] / (conv["ms"] * 1e-3) / 1e12 / pk["tf_sustained"],
+                                     "share_of_step": conv["ms"] / args.steps / step_ms}
+        lin = {f: gemm[f] - conv[f] for f in gemm}
+        roofline["linear_launches"] = {"launches_per_step": lin["launches"] / args.steps,
+                                       "avg_launch_us": lin["ms"] * 1e3 / max(1, lin["launches"]),
+                                       "achieved": lin["flops"] / (lin["ms"] * 1e-3) / 1e12 if lin["ms"] else 0.0,
+                                       "frac": (lin["flops"] / (lin["ms"] * 1e-3) / 1e12 / pk["tf_sustained"])
+                                       if lin["ms"] else 0.0,
+                                       "share_of_step": lin["ms"] / args.steps / step_ms}
     if "grads" in summ:
         s = summ["grads"]
         roofline["grads_kernel"] = {"bound": "hbm", "achieved": s["bytes"] / (s["ms"] * 1e-3) / 1e9, "peak": pk["hbm"],

@@ -99,13 +99,16 @@ class _ConvState:
         return hit
 
 
-def _gemm(x_nhwc, wk, has_bias, s1, s2, scale, T_out, Cout, geo, r, cdt):
+def _gemm(x_nhwc, wk, has_bias, s1, s2, scale, T_out, Cout, geo, r, cdt, kind="conv_fwd", c_alg=None):
+    """One implicit-GEMM launch.  `kind` / `c_alg` only label it for an installed launch profiler
+    (ops.PROFILER): "<kind>:<taps>", M = output pixels, K = taps * (algorithmic input channels), N = Cout."""
     N, H, W, C = x_nhwc.shape
     R, S, sh, sw, ph, pw, dh, dw = geo
     Ho = (H + 2 * ph - dh * (R - 1) - 1) // sh + 1
     Wo = (W + 2 * pw - dw * (S - 1) - 1) // sw + 1
     y = torch.empty((N, Ho, Wo, Cout), dtype=cdt, device=x_nhwc.device)
-    with torch.cuda.device(x_nhwc.device):
+    with torch.cuda.device(x_nhwc.device), ops._Prof(f"{kind}:{R * S}", N * Ho * Wo, R * S * (c_alg or C), Cout, r,
+                                                     x_nhwc.element_size()):
         rc = nat.lib().b200lora_conv2d_gemm(nat.ptr(x_nhwc), nat.ptr(wk), 1 if has_bias else 0, nat.ptr(s1),
                                             nat.ptr(s2), float(scale), nat.ptr(y), nat.ptr(T_out), N, H, W, C,
                                             Cout, R, S, sh, sw, ph, pw, dh, dw, r, nat.dtype_code(cdt),
@@ -180,7 +183,7 @@ class _LoraConv2dFn(torch.autograd.Function):
                 raise nat.B200LoraError("LoraInjectedConv2d backward needs padding <= (kernel-1)*dilation")
             zs1 = state.zeros(16 * R * S * Cz, cdt, dev)
             zs2 = state.zeros(Cin * 64, cdt, dev)
-            dxh = _gemm(Z, wb, False, zs1, zs2, 0.0, None, Cin, geo_b, r, cdt)
+            dxh = _gemm(Z, wb, False, zs1, zs2, 0.0, None, Cin, geo_b, r, cdt, kind="conv_bwd_dx", c_alg=Cout)
             dx = dxh.permute(0, 3, 1, 2)
             if dx.dtype != x_dtype:
                 dx = dx.to(x_dtype)
