@@ -244,7 +244,10 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
             if (xrole) {
               if (leader) mbar_arrive_expect_tx(&full_bar[s], main_tx);
               else mbar_arrive_cluster(full0);
-              if (p.conv)
+              if (p.conv == 2)      // whole-row tiles of a stride-1 convolution: one tiled 4-D box per tap
+                tma_load_4d_2sm(a_dst, &tmX, full0, cb * BK, cv_w + (tap % p.cv_S) * p.cv_dil_w,
+                                cv_h + (tap / p.cv_S) * p.cv_dil_h, cv_n, pol_x);
+              else if (p.conv)
                 tma_load_im2col_2sm(a_dst, &tmX, full0, cb * BK, cv_w, cv_h, cv_n,
                                     (uint16_t)((tap % p.cv_S) * p.cv_dil_w),
                                     (uint16_t)((tap / p.cv_S) * p.cv_dil_h), pol_x);

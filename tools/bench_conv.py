@@ -38,7 +38,11 @@ def timeit(fn, iters):
 ap = argparse.ArgumentParser()
 ap.add_argument("--r", type=int, default=16); ap.add_argument("--batch", type=int, default=8)
 ap.add_argument("--iters", type=int, default=20); ap.add_argument("--json", default=None)
+ap.add_argument("--hw", type=int, default=0, help="only the shapes at this spatial size (0 = all)")
+ap.add_argument("--no-torch", action="store_true", help="skip the stock arm (tile-width A/Bs via B200LORA_BN)")
 a = ap.parse_args()
+if a.hw:
+    SHAPES = [s for s in SHAPES if s[2] == a.hw]
 dev = torch.device("cuda:0"); dt = torch.bfloat16
 rows = []
 for (ci, co, H, ks, cnt) in SHAPES:
@@ -61,8 +65,10 @@ for (ci, co, H, ks, cnt) in SHAPES:
         mod(x).backward(dy)
     flops = 2.0 * a.batch * H * H * co * ci * ks * ks
     r_ = {"Cin": ci, "Cout": co, "H": H, "k": ks, "count": cnt,
-          "fwd_us": timeit(lambda: fwd(m), a.iters), "torch_fwd_us": timeit(lambda: fwd(st), a.iters),
-          "fwdbwd_us": timeit(lambda: fb(m), a.iters), "torch_fwdbwd_us": timeit(lambda: fb(st), a.iters)}
+          "fwd_us": timeit(lambda: fwd(m), a.iters),
+          "torch_fwd_us": float("nan") if a.no_torch else timeit(lambda: fwd(st), a.iters),
+          "fwdbwd_us": timeit(lambda: fb(m), a.iters),
+          "torch_fwdbwd_us": float("nan") if a.no_torch else timeit(lambda: fb(st), a.iters)}
     r_["fwd_tflops"] = flops / r_["fwd_us"] / 1e6
     r_["fwdbwd_tflops"] = 2 * flops / r_["fwdbwd_us"] / 1e6       # fwd + dX (W0 frozen: no dW)
     r_["speedup_fwd"] = r_["torch_fwd_us"] / r_["fwd_us"]; r_["speedup_fwdbwd"] = r_["torch_fwdbwd_us"] / r_["fwdbwd_us"]
