@@ -346,6 +346,9 @@ static int run_tc(const void* X, long long ldx, const void* W, long long ldw, bo
   return 0;
 }
 
+#ifndef B200LORA_SPLIT_B_DEFAULT
+#define B200LORA_SPLIT_B_DEFAULT 0
+#endif
 // CTA-pair variant (linear_tc2.cu): same math, tcgen05 cta_group::2, 256-row blocks per pair
 struct ConvGeoH { int N, H, W, C, Ho, Wo, R, S, str_h, str_w, pad_h, pad_w, dil_h, dil_w; };
 // X given as `n` tensors [M, cols] side by side along K (cols % 64 == 0, n <= 3)
@@ -382,6 +385,10 @@ static int run_tc2(const void* X, long long ldx, const void* W, long long ldw, b
     //               CCTL.IVALL per hand-off: +2..6 us per launch, measured);
     //   0           direct remote arrive with the default .cta scope (what round 1 shipped; CUTLASS's 2-SM pipelines
     //               do the same, but the PTX memory model does not order the peer's writes for the leader).
+    // B200LORA_SPLIT_B: the second TMA box of a CTA's B half on a third producer thread (warp 2)
+    static int sb = -1;
+    if (sb < 0) { const char* e = getenv("B200LORA_SPLIT_B"); sb = e ? (e[0] != '0' ? 1 : 0) : B200LORA_SPLIT_B_DEFAULT; }
+    p.split_b = sb;
     static int cs = -1;
     if (cs < 0) { const char* e = getenv("B200LORA_CLUSTER_SCOPE"); cs = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2; }
     p.cluster_scope = cs;

@@ -59,6 +59,8 @@ struct TcParams {
   int geglu_store_y;          // ... and still stores the pre-activation Y [M, 2*geglu] (needed by the backward)
   int out_f32;                // pair kernel: Y is an fp32 tensor (tmY: 16-column boxes): the accumulator is stored unrounded
                               // (backward dX of a layer whose input is fp32 under autocast: no bf16 -> fp32 cast launch)
+  int split_b;                // pair kernel: a CTA whose B half is two TMA boxes per k-block issues the second one from
+                              // warp 2 (third producer thread) instead of back to back on warp 3
   long long* dbg;             // optional clock64 timeline of CTA `dbg_cta` (tools/timeline.py)
   int dbg_cta;
 };

@@ -203,16 +203,24 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   pdl_wait();               // nothing above reads or writes global memory WRITTEN BY earlier kernels
   if (threadIdx.x == 0) TS2(0, 0, 1);
 
-  if (warp == 0 || warp == 3) {
+  // third producer (p.split_b): a CTA whose B half is TWO boxes per k-block (the peer's [W rows ; rank rows], the
+  // GEGLU leader's [hidden rows ; first gate rows]) issues the second box from warp 2, idle otherwise between the
+  // TMEM allocation and the teardown.  One thread sustains one {wait, issue} per ~350 cycles (tools/l2_ingest.cu), so
+  // two boxes on one thread held every k-block of the pair at ~700 cycles whatever the tile width.
+  const bool second_box = p.split_b && (GEGLU || !leader);
+  if (warp == 0 || warp == 3 || (warp == 2 && second_box)) {
     // =============================== TMA producers (both CTAs) ========================
-    // TMA issue is serial per thread (~130 cycles per cp.async.bulk.tensor): the loads of a stage
-    // are split over two threads.  warp 0 : the CTA's X rows + the arrive / expect_tx of the stage;
-    // warp 3 : the CTA's half of [W rows ; rank rows] and the tail blocks.
+    // TMA issue is serial per thread: the loads of a stage are split over two or three threads.
+    // warp 0 : the CTA's X rows + the arrive / expect_tx of the stage;
+    // warp 3 : the CTA's half of [W rows ; rank rows] and the tail blocks;
+    // warp 2 : the second box of that half, when there is one and p.split_b says so.
     {
       // the whole warp walks the schedule (warp-uniform control flow); one elected lane issues.
       // With `if (lane == 0)` around the loop ptxas wraps every uniform-datapath instruction
       // (UTMALDG / UTCHMMA / UTCBAR) in an ELECT + BRA.U.ANY convergence loop.
       const bool xrole = warp == 0;
+      const bool box1 = warp == 3;                                   // first (or only) box of the B half
+      const bool box2 = second_box ? warp == 2 : warp == 3;          // second box
       const uint64_t pol_x = policy_evict_normal();
       const uint64_t pol_w = policy_evict_last();
       int s = 0;
@@ -261,18 +269,18 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
               // peer's the other BN/2 - 8 gate rows (= H - 16: the usual box) and the rank rows.
               const int j0 = n_blk * (BN / 2);
               if (leader) {
-                tma_load_2d_2sm(b_dst, &tmX1, full0, kb * BK, j0, pol_w);
-                tma_load_2d_2sm(b_dst + (size_t)(BN / 2) * 128, &tmX2, full0, kb * BK, p.geglu + j0, pol_w);
+                if (box1) tma_load_2d_2sm(b_dst, &tmX1, full0, kb * BK, j0, pol_w);
+                if (box2) tma_load_2d_2sm(b_dst + (size_t)(BN / 2) * 128, &tmX2, full0, kb * BK, p.geglu + j0, pol_w);
               } else {
-                tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, p.geglu + j0 + 8, pol_w);
-                tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
+                if (box1) tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, p.geglu + j0 + 8, pol_w);
+                if (box2) tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
               }
             } else if (leader) {
               // B rows of the pair: [W n0 .. n0+BN) ; 16 rank rows], split in halves of H rows
-              if (kb >= w_done) tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);   // H rows
+              if (box1 && kb >= w_done) tma_load_2d_2sm(b_dst, &tmWh, full0, kb * BK, n0, pol_w);   // H rows
             } else {
-              if (kb >= w_done) tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, n0 + H, pol_w);   // H-16 rows
-              tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
+              if (box1 && kb >= w_done) tma_load_2d_2sm(b_dst, &tmWa, full0, kb * BK, n0 + H, pol_w);   // H-16 rows
+              if (box2) tma_load_2d_2sm(b_dst + (size_t)(H - RP) * 128, &tmS1, full0, kb * BK, 0, pol_w);
             }
           }
           __syncwarp();
@@ -282,14 +290,15 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
         }
       };
       auto load_tail = [&](int n_blk) {
-        mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);
+        if (warp != 2) mbar_wait(&empty_bar[s], ph ^ 1, S2_PROD_EMPTY);    // warp 2 has no part in a tail block: it
+                                                                           // only keeps its stage counter in step
         uint8_t* b_dst = stage_base + (size_t)s * stg_bytes + A_TILE_BYTES;
         const uint32_t full0 = full0_base + s * 8;
         if (elect_one()) {
           if (xrole) {
             if (leader) mbar_arrive_expect_tx(&full_bar[s], tail_tx);
             else mbar_arrive_cluster(full0);
-          } else {
+          } else if (box1) {
             const int s2_row = GEGLU ? n_blk * (BN / 2) + (int)rank * p.geglu      // leader: hidden rows, peer: gate rows
                                        : n_blk * BN + (int)rank * (BN / 2);
             tma_load_2d_2sm(b_dst, &tmS2, full0, 0, s2_row, pol_w);
