@@ -231,9 +231,9 @@ static int get_tmap_im2col(CUtensorMap* out, const void* ptr, int N, int H, int 
 
 // Stride-1 convolutions whose 128-pixel operand tiles are rectangles of the output image (whole rows of one
 // image, or whole images): the same tile as a tiled-mode 4-D box [64 channels, Wo, rows, images] of the NHWC
-// input, loaded at (c0, tap_w*dil - pad_w, oh0 + tap_h*dil - pad_h, n0) with the halo zero-filled.  The
-// im2col mode delivers ~23 B/clk/SM (measured: 0.37-0.43 us per k-block on every conv shape, whatever the
-// tile width); the tiled mode is the one the linear layers' X operand already streams at 4x that.
+// input, loaded at (c0, tap_w*dil - pad_w, oh0 + tap_h*dil - pad_h, n0) with the halo zero-filled.  Measured
+// equal to the im2col mode (1-3 % faster forward on the config-3 shapes): kept as the default
+// because it is the plain tiled form the linear layers' X operand uses.
 static bool conv_tiles_are_boxes(int Ho, int Wo, int str_h, int str_w, int* box_h, int* box_n) {
   if (str_h != 1 || str_w != 1 || Wo < 1 || Wo > 128 || 128 % Wo) return false;
   const int rows = 128 / Wo;

@@ -205,8 +205,8 @@ lora_gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
 
   // third producer (p.split_b): a CTA whose B half is TWO boxes per k-block (the peer's [W rows ; rank rows], the
   // GEGLU leader's [hidden rows ; first gate rows]) issues the second box from warp 2, idle otherwise between the
-  // TMEM allocation and the teardown.  One thread sustains one {wait, issue} per ~350 cycles (tools/l2_ingest.cu), so
-  // two boxes on one thread held every k-block of the pair at ~700 cycles whatever the tile width.
+  // TMEM allocation and the teardown.  One thread sustains one {wait, expect_tx, tensor load} per ~420 cycles
+  // (tools/l2_ingest.cu); off by default: measured equal on the conv shapes.
   const bool second_box = p.split_b && (GEGLU || !leader);
   if (warp == 0 || warp == 3 || (warp == 2 && second_box)) {
     // =============================== TMA producers (both CTAs) ========================

@@ -401,7 +401,7 @@ __device__ __forceinline__ void tma_load_im2col_2sm(void* smem_dst, const void* 
 // tiled-mode 4-D load of the same [128 pixels x 64 channels] operand tile as a BOX of the NHWC tensor
 // (channels, width, rows, images) at signed coordinates: out-of-image elements (the padding halo) are
 // zero-filled by the TMA unit.  Stride-1 convolutions whose 128-pixel tiles are whole image rows use it
-// instead of the im2col mode, which retires one pixel row per ~5.5 cycles (a quarter of the tiled rate).
+// instead of the im2col mode (measured equal: DESIGN.md 7.1).
 __device__ __forceinline__ void tma_load_4d_2sm(void* smem_dst, const void* tmap, uint32_t bar_cluster_addr,
                                                 int32_t c, int32_t w, int32_t h, int32_t n,
                                                 uint64_t cache_policy) {
